@@ -1,0 +1,152 @@
+/*
+ * star_flash_attn.h — C ABI of the B200-native attention forward / split-KV decode library
+ * (libStarFlashAttention.so).  Plain pointers and sizes only; no torch or C++ types.
+ *
+ * Every entry point is asynchronous on the CUDA stream it is given (a cudaStream_t passed as
+ * void*), allocates nothing in steady state and never synchronises the device, so a call can
+ * be captured in a CUDA graph.  Return value: 0 on success, a negative sfa_status otherwise;
+ * sfa_last_error() returns a thread-local message for the last failure.
+ *
+ * Which reference interface each function replaces (paths relative to the reference tree):
+ *   sfa_decoder_step   <- run_flash_decoder<half>(Flash_decoder_input&, Flash_decoder_params&,
+ *                         cudaStream_t)                       src/flash_attn.h:7-8, src/flash_attn.cu:937-1018
+ *                         and its Python face mha_fwd_cuda    src/flash_api.cpp:42-68
+ *   sfa_rotary_table   <- compute_rotary_table<half>          src/flash_attn.h:9-10, src/flash_attn.cu:531-538
+ *   sfa_fill           <- init_half_array                     src/flash_attn.h:11,   src/flash_attn.cu:502-510
+ *   sfa_decode         <- flash_decoder_kernel + flash_combine_kernel without the RoPE/append
+ *                         prologue, extended to GQA / bf16 / LSE        src/flash_attn.cu:554-935
+ *   sfa_fwd            <- no reference counterpart (the reference has no prefill kernel);
+ *                         softmax(QK^T*scale [+causal])V as in examples/python/testFlashDecoder.py:84-92
+ * The C++-mangled drop-in symbols (run_flash_decoder<half>, compute_rotary_table<half>,
+ * init_half_array) are exported from the same library; see include/src/flash_attn.h.
+ */
+#ifndef STAR_FLASH_ATTN_H_
+#define STAR_FLASH_ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SFA_ABI_VERSION 1
+
+typedef enum sfa_dtype { SFA_FP16 = 0, SFA_BF16 = 1 } sfa_dtype;
+
+typedef enum sfa_status {
+    SFA_OK = 0,
+    SFA_ERR_INVALID = -1,     /* bad argument (shape, alignment, dtype, null pointer)        */
+    SFA_ERR_UNSUPPORTED = -2, /* valid request this build has no kernel for (e.g. head_dim)  */
+    SFA_ERR_CUDA = -3,        /* a CUDA runtime/driver call failed; see sfa_last_error()     */
+    SFA_ERR_NO_DEVICE = -4    /* no sm_100 device: there is no CPU fallback                  */
+} sfa_status;
+
+/* ---------------------------------------------------------------- prefill forward ----------
+ * O = softmax(Q K^T * softmax_scale [+ causal mask]) V,  LSE = logsumexp of the scaled scores.
+ * q (batch, seqlen_q, heads_q, head_dim), k/v (batch, seqlen_k, heads_kv, head_dim), o like q;
+ * strides are in ELEMENTS; the head_dim axis is contiguous; every stride must be a multiple of
+ * 8 elements (16 bytes) and base pointers 16-byte aligned.  lse (batch, heads_q, seqlen_q)
+ * fp32 contiguous, may be NULL.  heads_q % heads_kv == 0 (GQA).  head_dim in {64, 128}.
+ * Causal mask is bottom-right aligned (query i sees keys j <= i + seqlen_k - seqlen_q).
+ * softmax_scale <= 0 selects 1/sqrt(head_dim). */
+typedef struct sfa_fwd_args {
+    const void* q;
+    const void* k;
+    const void* v;
+    void* o;
+    float* lse;
+    int32_t batch, seqlen_q, seqlen_k, heads_q, heads_kv, head_dim;
+    int64_t q_batch_stride, q_row_stride, q_head_stride;
+    int64_t k_batch_stride, k_row_stride, k_head_stride;
+    int64_t v_batch_stride, v_row_stride, v_head_stride;
+    int64_t o_batch_stride, o_row_stride, o_head_stride;
+    float softmax_scale;
+    int32_t causal;
+    int32_t dtype; /* sfa_dtype */
+} sfa_fwd_args;
+
+int sfa_fwd(const sfa_fwd_args* args, void* stream);
+
+/* ---------------------------------------------------------------- split-KV decode ----------
+ * One query token per sequence.  q (batch, heads_q, head_dim); k_cache/v_cache
+ * (batch, max_len, heads_kv, head_dim) addressed through element strides; seqlens int32
+ * (batch) = number of visible keys per sequence (NULL => seqlen_k for all); o like q;
+ * lse (batch, heads_q) fp32 or NULL.  heads_q / heads_kv in {1,2,4,8}.
+ * num_splits <= 0 lets the launcher choose.  workspace: device scratch of at least
+ * sfa_decode_workspace_bytes(...) bytes, or NULL to use the library's per-device grow-only
+ * buffer (grown with cudaMalloc outside graph capture only). */
+typedef struct sfa_decode_args {
+    const void* q;
+    const void* k_cache;
+    const void* v_cache;
+    const int32_t* seqlens;
+    void* o;
+    float* lse;
+    int32_t batch, seqlen_k, heads_q, heads_kv, head_dim;
+    int64_t q_batch_stride, q_head_stride;
+    int64_t k_batch_stride, k_row_stride, k_head_stride;
+    int64_t v_batch_stride, v_row_stride, v_head_stride;
+    int64_t o_batch_stride, o_head_stride;
+    float softmax_scale;
+    int32_t num_splits;
+    int32_t dtype; /* sfa_dtype */
+    void* workspace;
+    size_t workspace_bytes;
+} sfa_decode_args;
+
+int sfa_decode(const sfa_decode_args* args, void* stream);
+/* Number of splits the launcher would use for this shape (args->num_splits honoured if > 0). */
+int sfa_decode_num_splits(const sfa_decode_args* args);
+size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits);
+
+/* ---------------------------------------------------------------- drop-in decoder step -----
+ * The reference's run_flash_decoder with plain arguments.  For every sequence b:
+ * rotate q and k of the new token (interleaved pairs, position seq_len[b]) over the first
+ * rotary_dim dims, append k,v to layer idx_layer of the caches at row seq_len[b], and attend
+ * q over the seq_len[b]+1 cached keys with scale head_dim_inv.
+ * qkv (batch, 3, heads, head_dim) contiguous per token with row stride `qkv_stride` elements;
+ * caches (batch, num_layer, memory_max_len, heads, head_dim) contiguous; seq_len int32 (batch),
+ * each < memory_max_len; o (batch, heads, head_dim).  rotary_cos/sin: (memory_max_len,
+ * rotary_dim/2) tables in the data dtype, or both NULL to evaluate the angles in fp32.
+ * q/k/v biases are accepted and ignored, as in the reference (src/flash_api.cpp:18-32). */
+typedef struct sfa_decoder_step_args {
+    const void* qkv;
+    void* o;
+    const int32_t* seq_len;
+    void* k_cache_table;
+    void* v_cache_table;
+    const void* rotary_cos_table;
+    const void* rotary_sin_table;
+    float* lse; /* optional (batch, heads) */
+    int32_t batch_size, memory_max_len, num_heads, head_dim;
+    float head_dim_inv;
+    int32_t rotary_embedding_dim, qkv_stride, num_layer, idx_layer;
+    int32_t num_splits; /* <= 0: launcher's choice */
+    int32_t dtype;      /* sfa_dtype; the reference is fp16-only */
+} sfa_decoder_step_args;
+
+int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream);
+
+/* cos/sin tables (max_seq_len, rot_dim/2): angle = pos / 10000^(2i/rot_dim). */
+int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int32_t rot_dim,
+                     int32_t dtype, void* stream);
+/* Fill n elements with a constant (the reference's test utility). */
+int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream);
+
+/* ---------------------------------------------------------------- misc ---------------------- */
+const char* sfa_last_error(void);
+int sfa_abi_version(void);
+/* Number of kernels this library has launched in this process (all entry points). */
+uint64_t sfa_launch_count(void);
+/* Pipeline watchdog of the prefill kernel.  Its mbarrier waits are bounded (2 s); a wait that times
+ * out ends the kernel and latches a non-zero code here.  Synchronises the device; returns the code
+ * (0 = healthy) or a negative sfa_status, and clears the latch when `clear` is non-zero. */
+int sfa_fwd_watchdog(int clear);
+/* Releases the per-device workspaces (synchronises the device). */
+void sfa_release_workspaces(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STAR_FLASH_ATTN_H_ */

@@ -1,0 +1,111 @@
+"""ctypes binding of libStarFlashAttention.so (the C ABI declared in include/star_flash_attn.h).
+
+There is no CPU fallback: if the shared library has not been built, importing this module raises.
+Build it with ``python -m starflashattention_b200.build`` (or ``__graft_entry__.build()``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libStarFlashAttention.so")
+
+SFA_FP16, SFA_BF16 = 0, 1
+SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 0, -1, -2, -3, -4
+
+# Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
+EXPORTED_SYMBOLS = (
+    "sfa_fwd", "sfa_decode", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
+    "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
+    "sfa_fwd_watchdog", "sfa_release_workspaces",
+)
+# C++-mangled drop-ins of the reference's src/flash_attn.h:7-11.
+MANGLED_DROP_INS = (
+    "_Z17run_flash_decoderI6__halfEvR19Flash_decoder_inputR20Flash_decoder_paramsP11CUstream_st",
+    "_Z20compute_rotary_tableI6__halfEvPT_S2_ii",
+    "_Z15init_half_arrayP6__halfS_iii",
+)
+
+
+class FwdArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("o", C.c_void_p), ("lse", C.c_void_p),
+        ("batch", C.c_int32), ("seqlen_q", C.c_int32), ("seqlen_k", C.c_int32),
+        ("heads_q", C.c_int32), ("heads_kv", C.c_int32), ("head_dim", C.c_int32),
+        ("q_batch_stride", C.c_int64), ("q_row_stride", C.c_int64), ("q_head_stride", C.c_int64),
+        ("k_batch_stride", C.c_int64), ("k_row_stride", C.c_int64), ("k_head_stride", C.c_int64),
+        ("v_batch_stride", C.c_int64), ("v_row_stride", C.c_int64), ("v_head_stride", C.c_int64),
+        ("o_batch_stride", C.c_int64), ("o_row_stride", C.c_int64), ("o_head_stride", C.c_int64),
+        ("softmax_scale", C.c_float), ("causal", C.c_int32), ("dtype", C.c_int32),
+    ]
+
+
+class DecodeArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k_cache", C.c_void_p), ("v_cache", C.c_void_p), ("seqlens", C.c_void_p),
+        ("o", C.c_void_p), ("lse", C.c_void_p),
+        ("batch", C.c_int32), ("seqlen_k", C.c_int32), ("heads_q", C.c_int32), ("heads_kv", C.c_int32),
+        ("head_dim", C.c_int32),
+        ("q_batch_stride", C.c_int64), ("q_head_stride", C.c_int64),
+        ("k_batch_stride", C.c_int64), ("k_row_stride", C.c_int64), ("k_head_stride", C.c_int64),
+        ("v_batch_stride", C.c_int64), ("v_row_stride", C.c_int64), ("v_head_stride", C.c_int64),
+        ("o_batch_stride", C.c_int64), ("o_head_stride", C.c_int64),
+        ("softmax_scale", C.c_float), ("num_splits", C.c_int32), ("dtype", C.c_int32),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+    ]
+
+
+class DecoderStepArgs(C.Structure):
+    _fields_ = [
+        ("qkv", C.c_void_p), ("o", C.c_void_p), ("seq_len", C.c_void_p),
+        ("k_cache_table", C.c_void_p), ("v_cache_table", C.c_void_p),
+        ("rotary_cos_table", C.c_void_p), ("rotary_sin_table", C.c_void_p), ("lse", C.c_void_p),
+        ("batch_size", C.c_int32), ("memory_max_len", C.c_int32), ("num_heads", C.c_int32), ("head_dim", C.c_int32),
+        ("head_dim_inv", C.c_float),
+        ("rotary_embedding_dim", C.c_int32), ("qkv_stride", C.c_int32), ("num_layer", C.c_int32),
+        ("idx_layer", C.c_int32), ("num_splits", C.c_int32), ("dtype", C.c_int32),
+    ]
+
+
+class StarFlashAttentionError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libStarFlashAttention error {code}: {message}")
+        self.code = code
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing. Build it with `python -m starflashattention_b200.build`; "
+            "this package has no CPU or PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.sfa_fwd.argtypes = [C.POINTER(FwdArgs), C.c_void_p]
+    lib.sfa_fwd.restype = C.c_int
+    lib.sfa_decode.argtypes = [C.POINTER(DecodeArgs), C.c_void_p]
+    lib.sfa_decode.restype = C.c_int
+    lib.sfa_decode_num_splits.argtypes = [C.POINTER(DecodeArgs)]
+    lib.sfa_decode_num_splits.restype = C.c_int
+    lib.sfa_decode_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.sfa_decode_workspace_bytes.restype = C.c_size_t
+    lib.sfa_decoder_step.argtypes = [C.POINTER(DecoderStepArgs), C.c_void_p]
+    lib.sfa_decoder_step.restype = C.c_int
+    lib.sfa_rotary_table.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    lib.sfa_rotary_table.restype = C.c_int
+    lib.sfa_fill.argtypes = [C.c_void_p, C.c_float, C.c_int64, C.c_int32, C.c_void_p]
+    lib.sfa_fill.restype = C.c_int
+    lib.sfa_last_error.restype = C.c_char_p
+    lib.sfa_abi_version.restype = C.c_int
+    lib.sfa_launch_count.restype = C.c_uint64
+    lib.sfa_fwd_watchdog.argtypes = [C.c_int]
+    lib.sfa_fwd_watchdog.restype = C.c_int
+    lib.sfa_release_workspaces.restype = None
+    return lib
+
+
+lib = _load()
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise StarFlashAttentionError(rc, (lib.sfa_last_error() or b"").decode())

@@ -1,0 +1,251 @@
+// Entry points of libStarFlashAttention.so: the C ABI of include/star_flash_attn.h and the
+// C++-mangled drop-ins of the reference's src/flash_attn.h (run_flash_decoder<half>,
+// compute_rotary_table<half>, init_half_array) plus the typed additions.
+#include "internal.h"
+
+#include <math.h>
+#include <stdio.h>
+
+#include <src/flash_attn.h>
+
+namespace sfa {
+namespace {
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int check_dtype(int dtype) {
+    if (dtype != SFA_FP16 && dtype != SFA_BF16) return fail(SFA_ERR_INVALID, "dtype must be SFA_FP16 or SFA_BF16");
+    return SFA_OK;
+}
+
+int resolve_splits(int requested, int batch, int heads_kv, int max_len, int sm_count) {
+    if (requested > 0) return requested > 256 ? 256 : requested;
+    return choose_decode_splits(batch, heads_kv, max_len, sm_count);
+}
+
+int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream) {
+    int rc = check_dtype(a.dtype);
+    if (rc) return rc;
+    if (!a.q || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "decode: null tensor pointer");
+    if (a.batch < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0)
+        return fail(SFA_ERR_INVALID, "decode: negative or zero dimension");
+    if (a.heads_q % a.heads_kv) return fail(SFA_ERR_INVALID, "decode: heads_q must be a multiple of heads_kv");
+    const int64_t strides[] = {a.q_batch_stride, a.q_head_stride, a.k_batch_stride, a.k_row_stride, a.k_head_stride,
+                               a.v_batch_stride, a.v_row_stride, a.v_head_stride};
+    for (int64_t s : strides)
+        if (s % 8 != 0 || s < 0) return fail(SFA_ERR_INVALID, "decode: q/k/v strides must be non-negative multiples of 8 elements");
+    const uintptr_t ptrs[] = {(uintptr_t)a.q, (uintptr_t)a.k_cache, (uintptr_t)a.v_cache};
+    for (uintptr_t x : ptrs)
+        if (x % 16) return fail(SFA_ERR_INVALID, "decode: q/k/v base pointers must be 16-byte aligned");
+    if (a.batch == 0) return SFA_OK;
+    const DeviceInfo* dev = current_device();
+    if (!dev) return SFA_ERR_NO_DEVICE;
+
+    DecodeLaunch L;
+    L.q = a.q; L.k = a.k_cache; L.v = a.v_cache; L.seqlens = a.seqlens; L.o = a.o; L.lse = a.lse;
+    L.batch = a.batch; L.seqlen_k = a.seqlen_k; L.heads_q = a.heads_q; L.heads_kv = a.heads_kv; L.head_dim = a.head_dim;
+    L.q_bs = a.q_batch_stride; L.q_hs = a.q_head_stride;
+    L.k_bs = a.k_batch_stride; L.k_rs = a.k_row_stride; L.k_hs = a.k_head_stride;
+    L.v_bs = a.v_batch_stride; L.v_rs = a.v_row_stride; L.v_hs = a.v_head_stride;
+    L.o_bs = a.o_batch_stride; L.o_hs = a.o_head_stride;
+    L.scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
+    L.seqlen_add = seqlen_add;
+    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv, a.seqlen_k + seqlen_add, dev->sm_count);
+    L.dtype = a.dtype;
+    L.o_part = nullptr; L.ml_part = nullptr;
+    if (L.num_splits > 1) {
+        const size_t need = decode_workspace_bytes(a.batch, a.heads_q, a.head_dim, L.num_splits);
+        uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
+        if (ws) {
+            if (a.workspace_bytes < need) return fail(SFA_ERR_INVALID, "decode: workspace too small, need " + std::to_string(need) + " bytes");
+            if ((uintptr_t)ws % 16) return fail(SFA_ERR_INVALID, "decode: workspace must be 16-byte aligned");
+        } else {
+            ws = reinterpret_cast<uint8_t*>(get_workspace(need, stream));
+            if (!ws) return SFA_ERR_CUDA;
+        }
+        const size_t rows = (size_t)a.batch * a.heads_q * L.num_splits;
+        L.o_part = reinterpret_cast<float*>(ws);
+        L.ml_part = reinterpret_cast<float2*>(ws + align_up(rows * a.head_dim * sizeof(float), 16));
+    }
+    return launch_decode(L, stream);
+}
+
+int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
+    int rc = check_dtype(a.dtype);
+    if (rc) return rc;
+    if (!a.qkv || !a.o || !a.seq_len || !a.k_cache_table || !a.v_cache_table)
+        return fail(SFA_ERR_INVALID, "decoder step: null tensor pointer");
+    if (a.batch_size < 0 || a.memory_max_len <= 0 || a.num_heads <= 0 || a.num_layer <= 0 || a.idx_layer < 0 ||
+        a.idx_layer >= a.num_layer)
+        return fail(SFA_ERR_INVALID, "decoder step: bad dimension or layer index");
+    if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "decoder step: head_dim must be 64 or 128");
+    if (a.qkv_stride < 3 * a.num_heads * a.head_dim || a.qkv_stride % 8)
+        return fail(SFA_ERR_INVALID, "decoder step: qkv stride must be >= 3*num_heads*head_dim and a multiple of 8");
+    if (a.batch_size == 0) return SFA_OK;
+    const DeviceInfo* dev = current_device();
+    if (!dev) return SFA_ERR_NO_DEVICE;
+
+    const int B = a.batch_size, H = a.num_heads, D = a.head_dim;
+    const int splits = resolve_splits(a.num_splits, B, H, a.memory_max_len, dev->sm_count);
+    const size_t q_bytes = align_up((size_t)B * H * D * 2, 256);
+    const size_t part_bytes = decode_workspace_bytes(B, H, D, splits);
+    uint8_t* ws = reinterpret_cast<uint8_t*>(get_workspace(q_bytes + part_bytes, stream));
+    if (!ws) return SFA_ERR_CUDA;
+
+    RopeAppendLaunch R;
+    R.qkv = a.qkv; R.qkv_stride = a.qkv_stride; R.q_rot = ws;
+    R.k_cache = a.k_cache_table; R.v_cache = a.v_cache_table; R.seq_len = a.seq_len;
+    R.cos_table = a.rotary_cos_table; R.sin_table = a.rotary_sin_table;
+    R.batch = B; R.heads = H; R.head_dim = D; R.rotary_dim = a.rotary_embedding_dim; R.max_len = a.memory_max_len;
+    R.num_layer = a.num_layer; R.idx_layer = a.idx_layer; R.dtype = a.dtype;
+    if ((rc = launch_rope_append(R, stream))) return rc;
+
+    const int64_t layer_elems = (int64_t)a.memory_max_len * H * D;
+    sfa_decode_args d = {};
+    d.q = ws;
+    d.k_cache = reinterpret_cast<const uint8_t*>(a.k_cache_table) + 2 * layer_elems * a.idx_layer;
+    d.v_cache = reinterpret_cast<const uint8_t*>(a.v_cache_table) + 2 * layer_elems * a.idx_layer;
+    d.seqlens = a.seq_len; d.o = a.o; d.lse = a.lse;
+    d.batch = B; d.seqlen_k = a.memory_max_len - 1; d.heads_q = H; d.heads_kv = H; d.head_dim = D;
+    d.q_batch_stride = (int64_t)H * D; d.q_head_stride = D;
+    d.k_batch_stride = layer_elems * a.num_layer; d.k_row_stride = (int64_t)H * D; d.k_head_stride = D;
+    d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
+    d.o_batch_stride = (int64_t)H * D; d.o_head_stride = D;
+    d.softmax_scale = a.head_dim_inv;
+    d.num_splits = splits; d.dtype = a.dtype;
+    d.workspace = part_bytes ? ws + q_bytes : nullptr; d.workspace_bytes = part_bytes;
+    return decode_impl(d, /*seqlen_add=*/1, stream);
+}
+
+}  // namespace
+}  // namespace sfa
+
+// ============================================================================ C ABI
+extern "C" {
+
+int sfa_fwd(const sfa_fwd_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_fwd: null args");
+    return sfa::launch_fwd(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode(const sfa_decode_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode: null args");
+    return sfa::decode_impl(*args, 0, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode_num_splits(const sfa_decode_args* args) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_num_splits: null args");
+    const sfa::DeviceInfo* dev = sfa::current_device();
+    if (!dev) return SFA_ERR_NO_DEVICE;
+    return sfa::resolve_splits(args->num_splits, args->batch, args->heads_kv, args->seqlen_k, dev->sm_count);
+}
+
+size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits) {
+    return sfa::decode_workspace_bytes(batch, heads_q, head_dim, num_splits);
+}
+
+int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decoder_step: null args");
+    return sfa::decoder_step_impl(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int32_t rot_dim, int32_t dtype, void* stream) {
+    int rc = sfa::check_dtype(dtype);
+    if (rc) return rc;
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    return sfa::launch_rotary_table(cos_table, sin_table, max_seq_len, rot_dim, dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream) {
+    int rc = sfa::check_dtype(dtype);
+    if (rc) return rc;
+    return sfa::launch_fill(array, value, n, dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_fwd_watchdog(int clear) {
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return sfa::fail(SFA_ERR_CUDA, std::string("cudaDeviceSynchronize: ") + cudaGetErrorString(e));
+    int v = 0;
+    int rc = sfa::fwd_error_flag_read(&v);
+    if (rc) return rc;
+    if (clear && v) rc = sfa::fwd_error_flag_clear();
+    return rc ? rc : v;
+}
+
+}  // extern "C"
+
+// ============================================================================ C++ drop-ins
+namespace {
+template <typename T> struct DtypeOf;
+template <> struct DtypeOf<half> { static constexpr int value = SFA_FP16; };
+template <> struct DtypeOf<__nv_bfloat16> { static constexpr int value = SFA_BF16; };
+
+void report(const char* where, int rc) {
+    if (rc) fprintf(stderr, "[StarFlashAttention] %s failed (%d): %s\n", where, rc, sfa_last_error());
+}
+}  // namespace
+
+template <typename T>
+void run_flash_decoder(Flash_decoder_input& input, Flash_decoder_params& params, cudaStream_t stream) {
+    sfa_decoder_step_args a = {};
+    a.qkv = input.qkv; a.o = input.o; a.seq_len = reinterpret_cast<const int32_t*>(input.seq_len);
+    a.k_cache_table = input.k_cache_table; a.v_cache_table = input.v_cache_table;
+    a.rotary_cos_table = input.rotary_cos_table; a.rotary_sin_table = input.rotary_sin_table;
+    a.lse = input.lse;
+    a.batch_size = input.batch_size; a.memory_max_len = input.memory_max_len; a.num_heads = input.num_heads;
+    a.head_dim = input.head_dim;
+    a.head_dim_inv = input.head_dim_inv > 0.f ? input.head_dim_inv : 1.f / sqrtf((float)input.head_dim);
+    a.rotary_embedding_dim = input.rotary_embedding_dim;
+    a.qkv_stride = input.stride > 0 ? input.stride : 3 * input.num_heads * input.head_dim;
+    a.num_layer = input.num_layer > 0 ? input.num_layer : 1; a.idx_layer = input.idx_layer;
+    a.num_splits = params.num_splits;
+    a.dtype = DtypeOf<T>::value;
+    report("run_flash_decoder", sfa_decoder_step(&a, stream));
+}
+template void run_flash_decoder<half>(Flash_decoder_input&, Flash_decoder_params&, cudaStream_t);
+template void run_flash_decoder<__nv_bfloat16>(Flash_decoder_input&, Flash_decoder_params&, cudaStream_t);
+
+template <typename T>
+void compute_rotary_table(T* rotary_cos_table, T* rotary_sin_table, int max_seq_len, int rot_embed_dim) {
+    report("compute_rotary_table",
+           sfa_rotary_table(rotary_cos_table, rotary_sin_table, max_seq_len, rot_embed_dim, DtypeOf<T>::value, nullptr));
+}
+template void compute_rotary_table<half>(half*, half*, int, int);
+template void compute_rotary_table<__nv_bfloat16>(__nv_bfloat16*, __nv_bfloat16*, int, int);
+
+void init_half_array(half* array, half value, int n, int /*numBlocks*/, int /*blockSize*/) {
+    report("init_half_array", sfa_fill(array, __half2float(value), n, SFA_FP16, nullptr));
+}
+
+template <typename T>
+void run_flash_fwd(Flash_fwd_params& p, cudaStream_t stream) {
+    sfa_fwd_args a = {};
+    a.q = p.q; a.k = p.k; a.v = p.v; a.o = p.o; a.lse = p.lse;
+    a.batch = p.batch; a.seqlen_q = p.seqlen_q; a.seqlen_k = p.seqlen_k; a.heads_q = p.num_heads;
+    a.heads_kv = p.num_heads_k > 0 ? p.num_heads_k : p.num_heads; a.head_dim = p.head_dim;
+    a.q_batch_stride = p.q_batch_stride; a.q_row_stride = p.q_row_stride; a.q_head_stride = p.q_head_stride;
+    a.k_batch_stride = p.k_batch_stride; a.k_row_stride = p.k_row_stride; a.k_head_stride = p.k_head_stride;
+    a.v_batch_stride = p.v_batch_stride; a.v_row_stride = p.v_row_stride; a.v_head_stride = p.v_head_stride;
+    a.o_batch_stride = p.o_batch_stride; a.o_row_stride = p.o_row_stride; a.o_head_stride = p.o_head_stride;
+    a.softmax_scale = p.softmax_scale; a.causal = p.is_causal; a.dtype = DtypeOf<T>::value;
+    report("run_flash_fwd", sfa_fwd(&a, stream));
+}
+template void run_flash_fwd<half>(Flash_fwd_params&, cudaStream_t);
+template void run_flash_fwd<__nv_bfloat16>(Flash_fwd_params&, cudaStream_t);
+
+template <typename T>
+void run_flash_decode(Flash_decode_params& p, cudaStream_t stream) {
+    sfa_decode_args a = {};
+    a.q = p.q; a.k_cache = p.k_cache; a.v_cache = p.v_cache; a.seqlens = p.seqlens; a.o = p.o; a.lse = p.lse;
+    a.batch = p.batch; a.seqlen_k = p.seqlen_k; a.heads_q = p.num_heads;
+    a.heads_kv = p.num_heads_k > 0 ? p.num_heads_k : p.num_heads; a.head_dim = p.head_dim;
+    a.q_batch_stride = p.q_batch_stride; a.q_head_stride = p.q_head_stride;
+    a.k_batch_stride = p.k_batch_stride; a.k_row_stride = p.k_row_stride; a.k_head_stride = p.k_head_stride;
+    a.v_batch_stride = p.v_batch_stride; a.v_row_stride = p.v_row_stride; a.v_head_stride = p.v_head_stride;
+    a.o_batch_stride = p.o_batch_stride; a.o_head_stride = p.o_head_stride;
+    a.softmax_scale = p.softmax_scale; a.num_splits = p.num_splits; a.dtype = DtypeOf<T>::value;
+    report("run_flash_decode", sfa_decode(&a, stream));
+}
+template void run_flash_decode<half>(Flash_decode_params&, cudaStream_t);
+template void run_flash_decode<__nv_bfloat16>(Flash_decode_params&, cudaStream_t);

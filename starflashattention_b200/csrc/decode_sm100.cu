@@ -1,0 +1,339 @@
+// Split-KV decode attention (one query token per sequence) for sm_100a.
+//
+// Replaces the reference's flash_decoder_kernel / flash_combine_kernel pair
+// (reference src/flash_attn.cu:554-875 and :877-935) without the RoPE/append prologue, extended to
+// GQA, bf16, ragged sequence lengths and an LSE output.  HBM-bound: every K and V byte is read
+// exactly once, straight from global memory into tensor-core fragments, so there is no shared
+// memory staging on the streaming path at all.
+//
+// Work decomposition: grid (num_splits, heads_kv, batch), 4 warps per CTA.  A CTA owns one
+// contiguous chunk of one kv-head's keys and serves all heads_q/heads_kv query heads of its GQA
+// group, so K/V are read once per group.  Inside the CTA the warps take 16-key steps round robin;
+// each warp keeps a private online-softmax state (m, l, O) and the four states are merged through
+// shared memory at the end.
+//
+// Fragment trick: mma.sync.m16n8k16 with the query heads as the (zero padded) M rows.  A dot
+// product does not care about the order of its terms, so the head_dim axis is permuted such that
+// each thread's K fragment is one contiguous 16-byte load, and the output head_dim axis of P.V is
+// permuted such that each thread's V fragment comes from 16-byte loads too (two PRMTs per MMA).
+#include "internal.h"
+
+#include <math.h>
+
+namespace sfa {
+namespace {
+
+constexpr int kWarps = 4;
+constexpr int kStepKeys = 16;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+template <typename T>
+__device__ __forceinline__ void mma_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                          uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_16816<__half>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                                  uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                                         uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <typename T>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi);
+template <>
+__device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__device__ __forceinline__ uint32_t u4_word(const uint4& v, int i) {
+    return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w));
+}
+
+struct DecodeParams {
+    const void* q;
+    const void* k;
+    const void* v;
+    const int32_t* seqlens;
+    void* o;
+    float* lse;
+    float* o_part;
+    float2* ml_part;
+    int64_t q_bs, q_hs, k_bs, k_rs, k_hs, v_bs, v_rs, v_hs, o_bs, o_hs;
+    int seqlen_k, seqlen_add, heads_q, group, num_splits;
+    float scale_log2;
+};
+
+// Shared memory used only for the end-of-CTA merge of the four warp states.
+template <int D>
+struct MergeSmem {
+    float o[kWarps][8][D];
+    float m[kWarps][8];
+    float l[kWarps][8];
+};
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const DecodeParams p) {
+    constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
+    constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
+    __shared__ MergeSmem<D> sm;
+
+    const int split = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = lane >> 2, t = lane & 3;
+    const int g = p.group;
+
+    int len = (p.seqlens ? p.seqlens[b] : p.seqlen_k) + p.seqlen_add;
+    len = len < 0 ? 0 : len;
+    // Per-sequence chunking keeps ragged batches balanced across the splits.
+    const int chunk = (((len + p.num_splits - 1) / p.num_splits) + 63) & ~63;
+    const int k_begin = split * chunk;
+    const int k_end = min(len, k_begin + chunk);
+
+    // ---- query fragments (A operand), rows >= g are zero padding
+    uint32_t qa[NJ][4];
+    {
+        const T* qrow = reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_bs + (int64_t)(hk * g + r) * p.q_hs;
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+            uint4 w = make_uint4(0, 0, 0, 0);
+            if (r < g) w = *reinterpret_cast<const uint4*>(qrow + 32 * j + 8 * t);
+            qa[j][0] = w.x; qa[j][1] = w.y; qa[j][2] = w.z; qa[j][3] = w.w;
+        }
+    }
+
+    float o_acc[NH * 8][4];
+#pragma unroll
+    for (int i = 0; i < NH * 8; ++i) { o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f; }
+    float m_run = -INFINITY;   // running max (log2 domain), identical across the quad
+    float l_run = 0.f;         // this thread's share of the denominator
+
+    const T* kbase = reinterpret_cast<const T*>(p.k) + (int64_t)b * p.k_bs + (int64_t)hk * p.k_hs;
+    const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)b * p.v_bs + (int64_t)hk * p.v_hs;
+
+    for (int base = k_begin + warp * kStepKeys; base < k_end; base += kWarps * kStepKeys) {
+        const int last = k_end - 1;
+        // ---- issue every load of the step up front (16 x 16 B per thread at D=128)
+        uint4 kf[2][NJ];
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            const int key = min(base + 8 * nt + r, last);
+            const T* row = kbase + (int64_t)key * p.k_rs + 8 * t;
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) kf[nt][j] = ld_stream(row + 32 * j);
+        }
+        uint4 vf[4][NH];
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int key = min(base + 2 * t + (kk & 1) + 8 * (kk >> 1), last);
+            const T* row = vbase + (int64_t)key * p.v_rs + 8 * r;
+#pragma unroll
+            for (int h = 0; h < NH; ++h) vf[kk][h] = ld_stream(row + 64 * h);
+        }
+
+        // ---- S = Q K^T for two 8-key tiles
+        float s[2][4];
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                mma_16816<T>(s[nt], qa[j][0], 0u, qa[j][1], 0u, kf[nt][j].x, kf[nt][j].y);
+                mma_16816<T>(s[nt], qa[j][2], 0u, qa[j][3], 0u, kf[nt][j].z, kf[nt][j].w);
+            }
+        }
+        // ---- scale, mask the tail, online softmax (this thread: head r, keys base+8nt+2t+{0,1})
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                float x = s[nt][e] * p.scale_log2;
+                if (base + 8 * nt + 2 * t + e >= k_end) x = -INFINITY;
+                s[nt][e] = x;
+                mx = fmaxf(mx, x);
+            }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run, mx);           // finite: the step holds at least one live key
+        const float alpha = exp2f(m_run - m_new);       // 0 on the first step (m_run = -inf)
+        float psum = 0.f;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                s[nt][e] = exp2f(s[nt][e] - m_new);
+                psum += s[nt][e];
+            }
+        l_run = l_run * alpha + psum;
+        m_run = m_new;
+        if (__any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll
+            for (int i = 0; i < NH * 8; ++i) { o_acc[i][0] *= alpha; o_acc[i][1] *= alpha; }
+        }
+        // ---- O += P V
+        const uint32_t pa0 = pack2<T>(s[0][0], s[0][1]);   // keys 2t, 2t+1
+        const uint32_t pa2 = pack2<T>(s[1][0], s[1][1]);   // keys 2t+8, 2t+9
+#pragma unroll
+        for (int h = 0; h < NH; ++h)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t sel = (i & 1) ? 0x7632u : 0x5410u;
+                const uint32_t b0 = __byte_perm(u4_word(vf[0][h], i >> 1), u4_word(vf[1][h], i >> 1), sel);
+                const uint32_t b1 = __byte_perm(u4_word(vf[2][h], i >> 1), u4_word(vf[3][h], i >> 1), sel);
+                mma_16816<T>(o_acc[h * 8 + i], pa0, 0u, pa2, 0u, b0, b1);
+            }
+    }
+
+    // ---- merge the four warp states
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (r < g) {
+        if (t == 0) { sm.m[warp][r] = m_run; sm.l[warp][r] = l_run; }
+#pragma unroll
+        for (int h = 0; h < NH; ++h)
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) sm.o[warp][r][64 * h + 16 * t + 8 * e + i] = o_acc[h * 8 + i][e];
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < g * D; idx += kWarps * 32) {
+        const int hh = idx / D, d = idx - hh * D;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) M = fmaxf(M, sm.m[w][hh]);
+        float L = 0.f, acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            const float mw = sm.m[w][hh];
+            const float sc = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
+            L += sc * sm.l[w][hh];
+            acc += sc * sm.o[w][hh][d];
+        }
+        const int hq = hk * g + hh;
+        if (p.num_splits == 1) {
+            const float inv = L > 0.f ? 1.f / L : 0.f;
+            T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
+            orow[d] = (T)(acc * inv);
+            if (d == 0 && p.lse) p.lse[(int64_t)b * p.heads_q + hq] = L > 0.f ? (M + log2f(L)) * kLn2 : -INFINITY;
+        } else {
+            const int64_t row = ((int64_t)b * p.heads_q + hq) * p.num_splits + split;
+            p.o_part[row * D + d] = acc;
+            if (d == 0) p.ml_part[row] = make_float2(M, L);
+        }
+    }
+}
+
+// Merge of the per-split partials (reference flash_combine_kernel, src/flash_attn.cu:877-935, in fp32).
+template <typename T, int D>
+__global__ void __launch_bounds__(D) decode_combine_kernel(const DecodeParams p) {
+    extern __shared__ float w_sm[];   // num_splits weights
+    __shared__ float red[2];
+    const int hq = blockIdx.x, b = blockIdx.y;
+    const int64_t row0 = ((int64_t)b * p.heads_q + hq) * p.num_splits;
+    const int S = p.num_splits;
+    // Every thread scans the (m, l) pairs; S is a few dozen at most.
+    float M = -INFINITY;
+    for (int s = 0; s < S; ++s) M = fmaxf(M, p.ml_part[row0 + s].x);
+    float L = 0.f;
+    for (int s = threadIdx.x; s < S; s += D) {
+        const float2 ml = p.ml_part[row0 + s];
+        w_sm[s] = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - M);
+    }
+    __syncthreads();
+    for (int s = 0; s < S; ++s) L += w_sm[s] * p.ml_part[row0 + s].y;
+    float acc = 0.f;
+    const float* op = p.o_part + row0 * D + threadIdx.x;
+    for (int s = 0; s < S; ++s) acc += w_sm[s] * op[(int64_t)s * D];
+    const float inv = L > 0.f ? 1.f / L : 0.f;
+    T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
+    orow[threadIdx.x] = (T)(acc * inv);
+    if (threadIdx.x == 0 && p.lse) p.lse[(int64_t)b * p.heads_q + hq] = L > 0.f ? (M + log2f(L)) * kLn2 : -INFINITY;
+    (void)red;
+}
+
+template <typename T, int D>
+int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
+    dim3 grid(a.num_splits, a.heads_kv, a.batch);
+    decode_splitkv_kernel<T, D><<<grid, kWarps * 32, 0, stream>>>(p);
+    SFA_CUDA_CHECK(cudaGetLastError());
+    count_launch();
+    if (a.num_splits > 1) {
+        dim3 cgrid(a.heads_q, a.batch);
+        decode_combine_kernel<T, D><<<cgrid, D, a.num_splits * sizeof(float), stream>>>(p);
+        SFA_CUDA_CHECK(cudaGetLastError());
+        count_launch();
+    }
+    return SFA_OK;
+}
+
+}  // namespace
+
+// Splits heuristic: fill every SM with `waves` rounds of resident CTAs (3 per SM, see the launch
+// bounds), never cutting a sequence into chunks shorter than 256 keys.
+int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
+    static int waves = [] {
+        const char* e = getenv("SFA_DECODE_WAVES");
+        int w = e ? atoi(e) : 0;
+        return w > 0 ? w : 4;
+    }();
+    const long units = (long)batch * heads_kv;
+    const long slots = (long)sm_count * 3 * waves;
+    long s = (slots + units - 1) / units;
+    const long max_by_len = max_seqlen / 256 > 0 ? max_seqlen / 256 : 1;
+    if (s > max_by_len) s = max_by_len;
+    if (s > 128) s = 128;
+    if (s < 1) s = 1;
+    return (int)s;
+}
+
+size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits) {
+    if (num_splits <= 1) return 0;
+    const size_t rows = (size_t)batch * heads_q * num_splits;
+    return rows * head_dim * sizeof(float) + rows * sizeof(float2) + 256;
+}
+
+int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
+    if (a.heads_kv <= 0 || a.heads_q % a.heads_kv != 0) return fail(SFA_ERR_INVALID, "heads_q must be a multiple of heads_kv");
+    const int g = a.heads_q / a.heads_kv;
+    if (g > 8) return fail(SFA_ERR_UNSUPPORTED, "decode supports heads_q / heads_kv <= 8");
+    if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
+    if (a.batch == 0) return SFA_OK;
+    DecodeParams p;
+    p.q = a.q; p.k = a.k; p.v = a.v; p.seqlens = a.seqlens; p.o = a.o; p.lse = a.lse;
+    p.o_part = a.o_part; p.ml_part = a.ml_part;
+    p.q_bs = a.q_bs; p.q_hs = a.q_hs; p.k_bs = a.k_bs; p.k_rs = a.k_rs; p.k_hs = a.k_hs;
+    p.v_bs = a.v_bs; p.v_rs = a.v_rs; p.v_hs = a.v_hs; p.o_bs = a.o_bs; p.o_hs = a.o_hs;
+    p.seqlen_k = a.seqlen_k; p.seqlen_add = a.seqlen_add; p.heads_q = a.heads_q; p.group = g;
+    p.num_splits = a.num_splits;
+    p.scale_log2 = a.scale * kLog2e;
+    if (a.dtype == SFA_FP16) {
+        return a.head_dim == 128 ? launch_typed<__half, 128>(a, p, stream) : launch_typed<__half, 64>(a, p, stream);
+    }
+    return a.head_dim == 128 ? launch_typed<__nv_bfloat16, 128>(a, p, stream)
+                             : launch_typed<__nv_bfloat16, 64>(a, p, stream);
+}
+
+}  // namespace sfa

@@ -1,0 +1,506 @@
+// Prefill attention forward for sm_100a: O = softmax(Q K^T * scale [+ causal mask]) V, LSE.
+//
+// The reference has no prefill kernel; the arithmetic is the naive formula its
+// Python example runs (examples/python/testFlashDecoder.py:84 scores, :88 softmax, :92 probs @ V).
+//
+// Structure (one CTA per NQ x 128 query rows of one (batch, head)):
+//   warps 0 .. 4*NQ-1   softmax warpgroups, one per 128-row query tile; thread i of a warpgroup owns
+//                       row i (TMEM lane i): tcgen05.ld S -> online softmax in fp32 (exp2 on
+//                       log2e-prescaled scores, fused causal/tail masking) -> tcgen05.st P as
+//                       bf16/fp16 over the S columns -> epilogue O / l -> global
+//   warp 4*NQ           TMA producer: Q tiles once, then K_0 V_0 K_1 V_1 ... through a ring of
+//                       128-key tiles in shared memory (128-byte swizzle), mbarrier full/empty
+//   warp 4*NQ+1         tcgen05 issuer (one thread): S_q = Q_q K_j^T (SS, both operands K-major) and
+//                       O_q += P_q V_j (TS: A = P in TMEM, B = V in smem, MN-major); it also owns
+//                       the TMEM allocation
+// The two query tiles are interleaved in the issue order QK0_0 QK1_0 | PV0_0 QK0_1 | PV1_0 QK1_1 |
+// ... so that while one softmax warpgroup works on its S tile the tensor pipe runs the other
+// tile's MMAs (TMEM: S0 S1 O0 O1 = 4 x 128 columns at head_dim 128).
+// O is rescaled lazily: the reference maximum of a row only moves when the true maximum has grown
+// by more than 2^8, so the TMEM read-modify-write of O is rare after the first tiles.
+#include "internal.h"
+#include "sm100_ptx.cuh"
+
+#include <cuda.h>
+#include <limits.h>
+#include <math.h>
+#include <mutex>
+
+namespace sfa {
+namespace {
+
+using namespace ptx;
+
+constexpr int kBlockM = 128;        // query rows per tile (one TMEM lane each)
+constexpr int kBlockN = 128;        // keys per tile
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr float kRescaleThreshold = 8.0f;   // log2 units
+
+struct FwdParams {
+    void* o;
+    float* lse;
+    int* error_flag;
+    int64_t o_bs, o_rs, o_hs;
+    int seqlen_q, seqlen_k, heads_q, group;
+    int causal, is_bf16;
+    float scale_log2;
+};
+
+__device__ int g_fwd_error;   // set when an mbarrier wait times out (pipeline bug guard)
+
+// Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.
+__device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
+    if (mbar_try_wait(bar, parity)) return true;
+    const uint64_t t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++spins & 0xFF) == 0) {
+            if (*(volatile int*)error_flag != 0) return false;
+            if (global_timer_ns() - t0 > 2000000000ull) {
+                atomicCAS(error_flag, 0, code);
+                return false;
+            }
+        }
+    }
+    return true;
+}
+
+template <int D, int NQ, int NSTAGE>
+struct FwdSmem {
+    static constexpr int kSubTileBytes = kBlockM * 128;              // 128 rows x 64 elements x 2 B
+    static constexpr int kTileBytes = (D / 64) * kSubTileBytes;      // one 128 x D tile
+    static constexpr int kQOff = 0;
+    static constexpr int kRingOff = NQ * kTileBytes;
+    static constexpr int kBarOff = kRingOff + NSTAGE * kTileBytes;
+    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ], o_final[NQ]
+    static constexpr int kNumBars = 4 * NQ + 2 * NSTAGE;
+    static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
+    static constexpr int kBytes = kTmemPtrOff + 16;
+    static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
+};
+
+template <int D, int NQ, int NSTAGE>
+__global__ void __launch_bounds__(NQ == 2 ? 384 : 192, 1)
+fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
+           const __grid_constant__ CUtensorMap v_map, const FwdParams p) {
+    using L = FwdSmem<D, NQ, NSTAGE>;
+    constexpr int kSoftmaxWarps = 4 * NQ;
+    constexpr int kTmemCols = (NQ * (kBlockN + D)) <= 256 ? 256 : 512;
+    constexpr int kSub = D / 64;
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t bar_base = smem_base + L::kBarOff;
+    auto bar_q_full = [&](int q) { return bar_base + 8u * q; };
+    auto bar_kv_full = [&](int s) { return bar_base + 8u * (NQ + s); };
+    auto bar_kv_empty = [&](int s) { return bar_base + 8u * (NQ + NSTAGE + s); };
+    auto bar_s_full = [&](int q) { return bar_base + 8u * (NQ + 2 * NSTAGE + q); };
+    auto bar_p_ready = [&](int q) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + q); };
+    auto bar_o_final = [&](int q) { return bar_base + 8u * (3 * NQ + 2 * NSTAGE + q); };
+    volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // Heavy (late) query blocks first: under the causal mask they own the most key tiles.
+    const int m_block = gridDim.x - 1 - blockIdx.x;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int hk = h / p.group;
+    const int m0 = m_block * (NQ * kBlockM);
+    const int kv_tiles_total = (p.seqlen_k + kBlockN - 1) / kBlockN;
+    const int causal_shift = p.seqlen_k - p.seqlen_q;   // query i sees keys <= i + shift
+
+    // Key tiles each query tile needs (causal: up to the diagonal of its last row).
+    int n_tiles[NQ];
+    int n_max = 0;
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        int n = kv_tiles_total;
+        if (p.causal) {
+            const int last_row = min(m0 + (q + 1) * kBlockM, p.seqlen_q) - 1;
+            const int last_key = last_row + causal_shift;
+            n = last_key < 0 ? 0 : min(kv_tiles_total, last_key / kBlockN + 1);
+        }
+        if (m0 + q * kBlockM >= p.seqlen_q) n = 0;   // tile entirely past the end of Q
+        n_tiles[q] = n;
+        n_max = max(n_max, n);
+    }
+
+    if (warp == kSoftmaxWarps && lane == 0) {
+        prefetch_tensormap(&q_map);
+        prefetch_tensormap(&k_map);
+        prefetch_tensormap(&v_map);
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            mbar_init(bar_q_full(q), 1);
+            mbar_init(bar_s_full(q), 1);
+            mbar_init(bar_p_ready(q), 128);
+            mbar_init(bar_o_final(q), 1);
+        }
+#pragma unroll
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(bar_kv_full(s), 1);
+            mbar_init(bar_kv_empty(s), 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == kSoftmaxWarps + 1) {
+        tmem_alloc(smem_base + L::kTmemPtrOff, kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    // NQ == 2 runs three full warpgroups (the third holds the TMA and MMA warps plus two idle
+    // warps) so the register file can be re-split: the softmax warpgroups take what the others give up.
+    if (warp == kSoftmaxWarps) {
+        // =============================================================== TMA producer
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                if (n_tiles[q] == 0) continue;
+                mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
+#pragma unroll
+                for (int s = 0; s < kSub; ++s)
+                    tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
+                                64 * s, h, m0 + q * kBlockM, b);
+            }
+            for (int i = 0; i < 2 * n_max; ++i) {
+                const int slot = i % NSTAGE, use = i / NSTAGE;
+                if (!wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1)) break;
+                mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
+                const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+#pragma unroll
+                for (int s = 0; s < kSub; ++s)
+                    tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
+                                bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
+            }
+        }
+    } else if (warp == kSoftmaxWarps + 1) {
+        // =============================================================== tcgen05 issuer
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (lane == 0) {
+            const uint32_t idesc_qk = mma_idesc(p.is_bf16, 0, 0, kBlockM, kBlockN);
+            const uint32_t idesc_pv = mma_idesc(p.is_bf16, 0, 1, kBlockM, D);
+            // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
+            // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
+            constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
+            constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
+            bool ok = true;
+            auto issue_qk = [&](int q, int slot) {
+                const uint32_t q_addr = smem_base + L::kQOff + q * L::kTileBytes;
+                const uint32_t k_addr = smem_base + L::kRingOff + slot * L::kTileBytes;
+                const uint32_t s_tmem = tmem_base + q * kBlockN;
+#pragma unroll
+                for (int kc = 0; kc < D / 16; ++kc) {
+                    const uint32_t off = (kc >> 2) * L::kSubTileBytes + (kc & 3) * 32;
+                    mma_ss(s_tmem, smem_desc_at(desc_kmajor, q_addr + off), smem_desc_at(desc_kmajor, k_addr + off),
+                           idesc_qk, kc > 0);
+                }
+            };
+            auto issue_pv = [&](int q, int slot, bool accumulate) {
+                const uint32_t v_addr = smem_base + L::kRingOff + slot * L::kTileBytes;
+                const uint32_t p_tmem = tmem_base + q * kBlockN;
+                const uint32_t o_tmem = tmem_base + NQ * kBlockN + q * D;
+#pragma unroll
+                for (int kc = 0; kc < kBlockN / 16; ++kc)
+                    mma_ts(o_tmem, p_tmem + kc * 8, smem_desc_at(desc_v, v_addr + kc * 2048), idesc_pv,
+                           accumulate || kc > 0);
+            };
+            if (n_max > 0) {
+                ok = wait_barrier(bar_kv_full(0), 0, p.error_flag, 2);
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    if (!ok || n_tiles[q] == 0) continue;
+                    ok = wait_barrier(bar_q_full(q), 0, p.error_flag, 3);
+                    tc_fence_after();
+                    issue_qk(q, 0);
+                    tc_commit(bar_s_full(q));
+                }
+                tc_commit(bar_kv_empty(0));
+            }
+            for (int j = 0; j < n_max && ok; ++j) {
+                const int vi = 2 * j + 1, ki = 2 * j + 2;
+                const int vslot = vi % NSTAGE, kslot = ki % NSTAGE;
+                const bool have_next = j + 1 < n_max;
+                ok = wait_barrier(bar_kv_full(vslot), (vi / NSTAGE) & 1, p.error_flag, 4);
+                bool k_waited = false;
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    if (ok && j < n_tiles[q]) {
+                        ok = wait_barrier(bar_p_ready(q), j & 1, p.error_flag, 5);
+                        tc_fence_after();
+                        issue_pv(q, vslot, j > 0);
+                        if (j == n_tiles[q] - 1) tc_commit(bar_o_final(q));
+                    }
+                    if (q == NQ - 1) tc_commit(bar_kv_empty(vslot));
+                    if (ok && j + 1 < n_tiles[q]) {
+                        if (!k_waited) {
+                            ok = wait_barrier(bar_kv_full(kslot), (ki / NSTAGE) & 1, p.error_flag, 6);
+                            tc_fence_after();
+                            k_waited = true;
+                        }
+                        issue_qk(q, kslot);
+                        tc_commit(bar_s_full(q));
+                    }
+                    if (q == NQ - 1 && have_next) tc_commit(bar_kv_empty(kslot));
+                }
+            }
+        }
+    } else if (warp < kSoftmaxWarps) {
+        // =============================================================== softmax warpgroups
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int q = warp >> 2;
+        const int row_in_tile = (warp & 3) * 32 + lane;
+        const int row = m0 + q * kBlockM + row_in_tile;
+        const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        const uint32_t s_tmem = lane_base + q * kBlockN;
+        const uint32_t o_tmem = lane_base + NQ * kBlockN + q * D;
+        const int n_q = n_tiles[q];
+        const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
+        const float sl2 = p.scale_log2;
+
+        float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
+        float l_sum = 0.f;
+        bool ok = true;
+
+        for (int j = 0; j < n_q && ok; ++j) {
+            ok = wait_barrier(bar_s_full(q), j & 1, p.error_flag, 7);
+            tc_fence_after();
+            uint32_t su[kBlockN];
+#pragma unroll
+            for (int c = 0; c < kBlockN / 32; ++c) tmem_ld32(s_tmem + 32 * c, &su[32 * c]);
+            tmem_wait_ld();
+            float s[kBlockN];
+#pragma unroll
+            for (int c = 0; c < kBlockN; ++c) s[c] = __uint_as_float(su[c]);
+
+            const int key0 = j * kBlockN;
+            const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
+                                   (key0 + kBlockN > p.seqlen_k);
+            if (need_mask) {
+                const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay
+#pragma unroll
+                for (int c = 0; c < kBlockN; ++c)
+                    if (c > lim) s[c] = -INFINITY;
+            }
+            float mx = s[0];
+#pragma unroll
+            for (int c = 1; c < kBlockN; ++c) mx = fmaxf(mx, s[c]);
+
+            const float m_new = fmaxf(m_used, mx);
+            if (j == 0) {
+                m_used = m_new;
+            } else {
+                const bool grow = (m_new - m_used) * sl2 > kRescaleThreshold;   // false for -inf - -inf (NaN)
+                if (__any_sync(0xffffffffu, grow)) {
+                    const float alpha = grow ? ex2((m_used - m_new) * sl2) : 1.f;
+                    l_sum *= alpha;
+                    if (grow) m_used = m_new;
+#pragma unroll
+                    for (int c = 0; c < D / 32; ++c) {
+                        uint32_t o[32];
+                        tmem_ld32(o_tmem + 32 * c, o);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st32(o_tmem + 32 * c, o);
+                    }
+                }
+            }
+            const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
+            uint32_t pk[kBlockN / 2];
+#pragma unroll
+            for (int c = 0; c < kBlockN; c += 2) {
+                const float p0 = ex2(fmaf(s[c], sl2, neg_m));
+                const float p1 = ex2(fmaf(s[c + 1], sl2, neg_m));
+                l_sum += p0 + p1;
+                if (p.is_bf16) {
+                    __nv_bfloat162 v = __floats2bfloat162_rn(p0, p1);
+                    pk[c / 2] = *reinterpret_cast<uint32_t*>(&v);
+                } else {
+                    __half2 v = __floats2half2_rn(p0, p1);
+                    pk[c / 2] = *reinterpret_cast<uint32_t*>(&v);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < kBlockN / 64; ++c) tmem_st32(s_tmem + 32 * c, &pk[32 * c]);
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar_p_ready(q));
+        }
+
+        // ---- epilogue: O / l -> global, LSE
+        const bool row_ok = row < p.seqlen_q;
+        const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
+        uint8_t* o_row = reinterpret_cast<uint8_t*>(p.o) +
+                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs);
+        if (n_q > 0 && ok) ok = wait_barrier(bar_o_final(q), 0, p.error_flag, 8);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            if (n_q > 0) {
+                tmem_ld32(o_tmem + 32 * c, o);
+                tmem_wait_ld();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = 0u;
+            }
+            uint32_t packed[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float a = __uint_as_float(o[2 * i]) * inv_l, c2 = __uint_as_float(o[2 * i + 1]) * inv_l;
+                if (p.is_bf16) {
+                    __nv_bfloat162 v = __floats2bfloat162_rn(a, c2);
+                    packed[i] = *reinterpret_cast<uint32_t*>(&v);
+                } else {
+                    __half2 v = __floats2half2_rn(a, c2);
+                    packed[i] = *reinterpret_cast<uint32_t*>(&v);
+                }
+            }
+            if (row_ok) {
+                uint4* dst = reinterpret_cast<uint4*>(o_row + 64 * c);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+            }
+        }
+        if (row_ok && p.lse) {
+            const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
+            p.lse[((int64_t)b * p.heads_q + h) * p.seqlen_q + row] = lse;
+        }
+    }
+
+    else {
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");   // idle warps of the third warpgroup
+    }
+
+    // ---- teardown: every tcgen05 operation of this CTA has completed once the softmax warps are here
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kSoftmaxWarps + 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            ptr = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(ptr);
+    }();
+    return fn;
+}
+
+// (head_dim, heads, rows, batch) view of a (batch, rows, heads, head_dim) strided tensor, boxes of
+// 64 x 1 x 128 x 1 elements with the 128-byte swizzle the UMMA descriptors expect.
+int make_map(CUtensorMap* map, const void* base, int dtype, int head_dim, int heads, int rows, int batch,
+             int64_t head_stride, int64_t row_stride, int64_t batch_stride) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail(SFA_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[4] = {(cuuint64_t)head_dim, (cuuint64_t)heads, (cuuint64_t)rows, (cuuint64_t)batch};
+    cuuint64_t strides[3] = {(cuuint64_t)head_stride * 2, (cuuint64_t)row_stride * 2, (cuuint64_t)batch_stride * 2};
+    // A dimension of extent 1 may carry any stride; keep the encoder's 16-byte rule satisfied.
+    for (int i = 0; i < 3; ++i)
+        if (strides[i] == 0) strides[i] = 16;
+    cuuint32_t box[4] = {64, 1, (cuuint32_t)kBlockM, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, dtype == SFA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SFA_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return SFA_OK;
+}
+
+template <int D, int NQ, int NSTAGE>
+int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p,
+                    int batch, cudaStream_t stream) {
+    using L = FwdSmem<D, NQ, NSTAGE>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE>;
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(once, [&] {
+        attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kAlloc);
+    });
+    SFA_CUDA_CHECK(attr_err);
+    const int m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
+    dim3 grid(m_blocks, p.heads_q, batch);
+    kern<<<grid, NQ == 2 ? 384 : 192, L::kAlloc, stream>>>(qm, km, vm, p);
+    SFA_CUDA_CHECK(cudaGetLastError());
+    count_launch();
+    return SFA_OK;
+}
+
+}  // namespace
+
+int fwd_error_flag_read(int* value) {
+    SFA_CUDA_CHECK(cudaMemcpyFromSymbol(value, g_fwd_error, sizeof(int)));
+    return SFA_OK;
+}
+int fwd_error_flag_clear() {
+    const int zero = 0;
+    SFA_CUDA_CHECK(cudaMemcpyToSymbol(g_fwd_error, &zero, sizeof(int)));
+    return SFA_OK;
+}
+
+int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
+    if (!a.q || !a.k || !a.v || !a.o) return fail(SFA_ERR_INVALID, "fwd: null tensor pointer");
+    if (a.batch < 0 || a.seqlen_q < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0)
+        return fail(SFA_ERR_INVALID, "fwd: negative or zero dimension");
+    if (a.heads_q % a.heads_kv) return fail(SFA_ERR_INVALID, "fwd: heads_q must be a multiple of heads_kv");
+    if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "fwd: head_dim must be 64 or 128");
+    if (a.dtype != SFA_FP16 && a.dtype != SFA_BF16) return fail(SFA_ERR_INVALID, "fwd: dtype must be fp16 or bf16");
+    const int64_t strides[] = {a.q_batch_stride, a.q_row_stride, a.q_head_stride, a.k_batch_stride, a.k_row_stride,
+                               a.k_head_stride, a.v_batch_stride, a.v_row_stride, a.v_head_stride, a.o_batch_stride,
+                               a.o_row_stride, a.o_head_stride};
+    for (int64_t s : strides)
+        if (s % 8 != 0 || s < 0) return fail(SFA_ERR_INVALID, "fwd: every stride must be a non-negative multiple of 8 elements");
+    const uintptr_t ptrs[] = {(uintptr_t)a.q, (uintptr_t)a.k, (uintptr_t)a.v, (uintptr_t)a.o};
+    for (uintptr_t x : ptrs)
+        if (x % 16) return fail(SFA_ERR_INVALID, "fwd: tensor base pointers must be 16-byte aligned");
+    if (a.batch == 0 || a.seqlen_q == 0) return SFA_OK;
+    const DeviceInfo* dev = current_device();
+    if (!dev) return SFA_ERR_NO_DEVICE;
+
+    alignas(64) CUtensorMap qm, km, vm;
+    int rc;
+    // seqlen_k == 0 still needs valid maps; a one-row extent keeps the encoder happy and is never read.
+    const int rows_k = a.seqlen_k > 0 ? a.seqlen_k : 1;
+    if ((rc = make_map(&qm, a.q, a.dtype, a.head_dim, a.heads_q, a.seqlen_q, a.batch, a.q_head_stride, a.q_row_stride, a.q_batch_stride))) return rc;
+    if ((rc = make_map(&km, a.k, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.k_head_stride, a.k_row_stride, a.k_batch_stride))) return rc;
+    if ((rc = make_map(&vm, a.v, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.v_head_stride, a.v_row_stride, a.v_batch_stride))) return rc;
+
+    FwdParams p;
+    p.o = a.o; p.lse = a.lse;
+    p.o_bs = a.o_batch_stride; p.o_rs = a.o_row_stride; p.o_hs = a.o_head_stride;
+    p.seqlen_q = a.seqlen_q; p.seqlen_k = a.seqlen_k; p.heads_q = a.heads_q; p.group = a.heads_q / a.heads_kv;
+    p.causal = a.causal ? 1 : 0; p.is_bf16 = a.dtype == SFA_BF16;
+    const float scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
+    p.scale_log2 = scale * kLog2e;
+    void* flag_addr = nullptr;
+    SFA_CUDA_CHECK(cudaGetSymbolAddress(&flag_addr, g_fwd_error));
+    p.error_flag = reinterpret_cast<int*>(flag_addr);
+
+    static int forced_nq = [] { const char* e = getenv("SFA_FWD_NQ"); return e ? atoi(e) : 0; }();
+    const int nq = forced_nq == 1 || forced_nq == 2 ? forced_nq : (a.seqlen_q > kBlockM ? 2 : 1);
+    if (a.head_dim == 128)
+        return nq == 2 ? launch_instance<128, 2, 4>(qm, km, vm, p, a.batch, stream)
+                       : launch_instance<128, 1, 4>(qm, km, vm, p, a.batch, stream);
+    return nq == 2 ? launch_instance<64, 2, 6>(qm, km, vm, p, a.batch, stream)
+                   : launch_instance<64, 1, 6>(qm, km, vm, p, a.batch, stream);
+}
+
+}  // namespace sfa

@@ -1,0 +1,74 @@
+// Internal host-side contracts between the translation units of libStarFlashAttention.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+
+#include "../../include/star_flash_attn.h"
+
+namespace sfa {
+
+// Thread-local error string behind sfa_last_error().
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+void count_launch(int n = 1);
+
+struct DeviceInfo {
+    int device = -1;
+    int sm_count = 0;
+    int cc_major = 0, cc_minor = 0;
+};
+// Cached per-device properties; returns nullptr (and sets the error) when no sm_100 device is current.
+const DeviceInfo* current_device();
+
+// Per-device grow-only scratch (never shrinks; grown only outside stream capture).
+void* get_workspace(size_t bytes, cudaStream_t stream);
+
+#define SFA_CUDA_CHECK(expr)                                                                  \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return ::sfa::fail(SFA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+// ------------------------------------------------------------------ decode (decode_sm100.cu)
+struct DecodeLaunch {
+    const void* q; const void* k; const void* v; const int32_t* seqlens;
+    void* o; float* lse;
+    int batch, seqlen_k, heads_q, heads_kv, head_dim;
+    int64_t q_bs, q_hs, k_bs, k_rs, k_hs, v_bs, v_rs, v_hs, o_bs, o_hs;
+    float scale;
+    int seqlen_add;          // added to every sequence length (1 for the decoder step: the appended token)
+    int num_splits;          // resolved (>= 1)
+    float* o_part;           // (B,Hq,S,D) fp32   (unused when num_splits == 1)
+    float2* ml_part;         // (B,Hq,S)  (m in log2 domain, l)
+    int dtype;
+};
+int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count);
+size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits);
+int launch_decode(const DecodeLaunch& p, cudaStream_t stream);
+
+// ------------------------------------------------------------------ rope / cache (rope_cache.cu)
+struct RopeAppendLaunch {
+    const void* qkv; int qkv_stride;
+    void* q_rot;                       // (B,H,D) rotated queries
+    void* k_cache; void* v_cache;      // (B,L,M,H,D)
+    const int32_t* seq_len;
+    const void* cos_table; const void* sin_table;
+    int batch, heads, head_dim, rotary_dim, max_len, num_layer, idx_layer;
+    int dtype;
+};
+int launch_rope_append(const RopeAppendLaunch& p, cudaStream_t stream);
+int launch_rotary_table(void* cos_t, void* sin_t, int max_seq_len, int rot_dim, int dtype, cudaStream_t stream);
+int launch_fill(void* arr, float value, int64_t n, int dtype, cudaStream_t stream);
+
+// ------------------------------------------------------------------ prefill (fwd_sm100.cu)
+int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream);
+// Pipeline watchdog of the prefill kernel: non-zero after an mbarrier wait timed out.
+int fwd_error_flag_read(int* value);
+int fwd_error_flag_clear();
+
+}  // namespace sfa

@@ -1,0 +1,226 @@
+"""Host-side mirror of the reference's operator interface, on top of the C ABI.
+
+* ``mha_fwd_cuda``          <- ``star_flash_attn.mha_fwd_cuda`` (reference src/flash_api.cpp:42-68, bound at :74-79):
+                               same positional arguments, ``o`` written in place and returned, biases accepted
+                               and ignored, work queued on the current CUDA stream.
+* ``compute_rotary_table``  <- ``compute_rotary_table<half>`` (reference src/flash_attn.cu:531-538)
+* ``init_half_array``       <- ``init_half_array`` (reference src/flash_attn.cu:502-510)
+* ``fwd`` / ``decode``      additions: prefill forward and GQA/bf16 split-KV decode with LSE (no reference
+                               counterpart; arithmetic of examples/python/testFlashDecoder.py:84-92).
+
+PyTorch is used for device memory and streams only; every computation happens in libStarFlashAttention.so.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Tuple
+
+import torch
+
+from . import _capi
+from ._capi import DecodeArgs, DecoderStepArgs, FwdArgs, check, lib
+
+__all__ = ["fwd", "decode", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
+           "launch_count", "decode_num_splits"]
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float16:
+        return _capi.SFA_FP16
+    if t.dtype == torch.bfloat16:
+        return _capi.SFA_BF16
+    raise TypeError(f"only float16 and bfloat16 are supported, got {t.dtype}")
+
+
+def _require_cuda(*tensors: torch.Tensor) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise ValueError("all tensors must live on a CUDA device (there is no CPU fallback)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise ValueError("all tensors must be on the same device")
+    return dev
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = False,
+        softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
+        return_lse: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """O = softmax(Q K^T * scale [+ causal]) V.  q (B,Sq,Hq,D); k, v (B,Sk,Hkv,D); last dim contiguous.
+
+    Returns (out like q, lse (B,Hq,Sq) float32 or None).  Causal mask is bottom-right aligned.
+    """
+    dev = _require_cuda(q, k, v, out)
+    if q.dim() != 4 or k.dim() != 4 or v.dim() != 4:
+        raise ValueError("q, k, v must be 4-D (batch, seqlen, heads, head_dim)")
+    B, Sq, Hq, D = q.shape
+    Bk, Sk, Hkv, Dk = k.shape
+    if v.shape != k.shape or Bk != B or Dk != D:
+        raise ValueError("k and v must have equal shapes matching q's batch and head_dim")
+    if q.dtype != k.dtype or q.dtype != v.dtype:
+        raise TypeError("q, k, v must share one dtype")
+    for t in (q, k, v):
+        if t.stride(-1) != 1:
+            raise ValueError("the head_dim axis must be contiguous")
+    if out is None:
+        out = torch.empty((B, Sq, Hq, D), dtype=q.dtype, device=dev)
+    elif out.shape != q.shape or out.dtype != q.dtype or out.stride(-1) != 1:
+        raise ValueError("out must look like q")
+    lse = torch.empty((B, Hq, Sq), dtype=torch.float32, device=dev) if return_lse else None
+    a = FwdArgs()
+    a.q, a.k, a.v, a.o = q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr()
+    a.lse = lse.data_ptr() if lse is not None else None
+    a.batch, a.seqlen_q, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = B, Sq, Sk, Hq, Hkv, D
+    a.q_batch_stride, a.q_row_stride, a.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
+    a.k_batch_stride, a.k_row_stride, a.k_head_stride = k.stride(0), k.stride(1), k.stride(2)
+    a.v_batch_stride, a.v_row_stride, a.v_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    a.o_batch_stride, a.o_row_stride, a.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
+    a.causal = 1 if causal else 0
+    a.dtype = _dtype_code(q)
+    with torch.cuda.device(dev):
+        check(lib.sfa_fwd(a, _stream()))
+    return out, lse
+
+
+def _decode_args(q, k_cache, v_cache, seqlens, out, lse, softmax_scale, num_splits) -> DecodeArgs:
+    B, Hq, D = q.shape
+    _, M, Hkv, _ = k_cache.shape
+    a = DecodeArgs()
+    a.q, a.k_cache, a.v_cache = q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr()
+    a.seqlens = seqlens.data_ptr() if seqlens is not None else None
+    a.o = out.data_ptr()
+    a.lse = lse.data_ptr() if lse is not None else None
+    a.batch, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = B, M, Hq, Hkv, D
+    a.q_batch_stride, a.q_head_stride = q.stride(0), q.stride(1)
+    a.k_batch_stride, a.k_row_stride, a.k_head_stride = k_cache.stride(0), k_cache.stride(1), k_cache.stride(2)
+    a.v_batch_stride, a.v_row_stride, a.v_head_stride = v_cache.stride(0), v_cache.stride(1), v_cache.stride(2)
+    a.o_batch_stride, a.o_head_stride = out.stride(0), out.stride(1)
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
+    a.num_splits = int(num_splits)
+    a.dtype = _dtype_code(q)
+    a.workspace, a.workspace_bytes = None, 0
+    return a
+
+
+def decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+           seqlens: Optional[torch.Tensor] = None, softmax_scale: Optional[float] = None,
+           num_splits: int = 0, out: Optional[torch.Tensor] = None,
+           return_lse: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Single-token attention over a KV cache.  q (B,Hq,D); caches (B,M,Hkv,D); seqlens int32 (B) or None."""
+    dev = _require_cuda(q, k_cache, v_cache, seqlens, out)
+    if q.dim() != 3 or k_cache.dim() != 4 or v_cache.shape != k_cache.shape:
+        raise ValueError("q must be (batch, heads, head_dim); caches (batch, max_len, heads_kv, head_dim)")
+    if q.shape[0] != k_cache.shape[0] or q.shape[2] != k_cache.shape[3]:
+        raise ValueError("batch / head_dim mismatch between q and the caches")
+    if q.dtype != k_cache.dtype or q.dtype != v_cache.dtype:
+        raise TypeError("q and the caches must share one dtype")
+    for t in (q, k_cache, v_cache):
+        if t.stride(-1) != 1:
+            raise ValueError("the head_dim axis must be contiguous")
+    if seqlens is not None and (seqlens.dtype != torch.int32 or seqlens.numel() != q.shape[0] or not seqlens.is_contiguous()):
+        raise ValueError("seqlens must be a contiguous int32 tensor of shape (batch,)")
+    if out is None:
+        out = torch.empty_like(q, memory_format=torch.contiguous_format)
+    elif out.shape != q.shape or out.dtype != q.dtype or out.stride(-1) != 1:
+        raise ValueError("out must look like q")
+    lse = torch.empty(q.shape[:2], dtype=torch.float32, device=dev) if return_lse else None
+    a = _decode_args(q, k_cache, v_cache, seqlens, out, lse, softmax_scale, num_splits)
+    with torch.cuda.device(dev):
+        check(lib.sfa_decode(a, _stream()))
+    return out, lse
+
+
+def decode_num_splits(batch: int, seqlen_k: int, heads_kv: int, device=None) -> int:
+    """Number of KV splits the launcher picks for this shape on the current device."""
+    a = DecodeArgs()
+    a.batch, a.seqlen_k, a.heads_kv, a.num_splits = batch, seqlen_k, heads_kv, 0
+    with torch.cuda.device(device if device is not None else torch.cuda.current_device()):
+        n = lib.sfa_decode_num_splits(a)
+    if n < 0:
+        check(n)
+    return n
+
+
+def mha_fwd_cuda(qkv: torch.Tensor, q_bias, k_bias, v_bias, k_cache_table: torch.Tensor,
+                 v_cache_table: torch.Tensor, seq_len: torch.Tensor, o: torch.Tensor, batch_size: int,
+                 memory_max_len: int, num_heads: int, head_dim: int, rotary_embedding_dim: int,
+                 max_input_length: int, num_layer: int, idx_layer: int, *,
+                 rotary_cos_table: Optional[torch.Tensor] = None, rotary_sin_table: Optional[torch.Tensor] = None,
+                 lse: Optional[torch.Tensor] = None, num_splits: int = 0) -> torch.Tensor:
+    """One decoder step: RoPE(q, k) at position seq_len[b], append k, v to layer ``idx_layer`` of the caches,
+    attend q over the seq_len[b]+1 cached keys.  Mirrors the reference entry argument for argument
+    (src/flash_api.cpp:42-58); the keyword-only arguments are additions."""
+    dev = _require_cuda(qkv, k_cache_table, v_cache_table, seq_len, o, rotary_cos_table, rotary_sin_table, lse)
+    if seq_len.dtype != torch.int32 or not seq_len.is_contiguous() or seq_len.numel() != batch_size:
+        raise ValueError("seq_len must be a contiguous int32 tensor of shape (batch_size,)")
+    want_cache = (batch_size, num_layer, memory_max_len, num_heads, head_dim)
+    if tuple(k_cache_table.shape) != want_cache or tuple(v_cache_table.shape) != want_cache:
+        raise ValueError(f"caches must have shape {want_cache}")
+    if not (k_cache_table.is_contiguous() and v_cache_table.is_contiguous() and o.is_contiguous()):
+        raise ValueError("caches and o must be contiguous")
+    if tuple(qkv.shape) != (batch_size, 3, num_heads, head_dim) or qkv.stride(-1) != 1 or \
+            qkv.stride(2) != head_dim or qkv.stride(1) != num_heads * head_dim:
+        raise ValueError("qkv must be (batch_size, 3, num_heads, head_dim) with a dense token row")
+    if tuple(o.shape) != (batch_size, num_heads, head_dim):
+        raise ValueError("o must be (batch_size, num_heads, head_dim)")
+    if not (qkv.dtype == k_cache_table.dtype == v_cache_table.dtype == o.dtype):
+        raise TypeError("qkv, caches and o must share one dtype")
+    for t in (rotary_cos_table, rotary_sin_table):
+        if t is not None and (t.dtype != qkv.dtype or not t.is_contiguous() or
+                              tuple(t.shape) != (memory_max_len, rotary_embedding_dim // 2)):
+            raise ValueError("rotary tables must be contiguous (memory_max_len, rotary_embedding_dim/2) in the data dtype")
+    a = DecoderStepArgs()
+    a.qkv, a.o, a.seq_len = qkv.data_ptr(), o.data_ptr(), seq_len.data_ptr()
+    a.k_cache_table, a.v_cache_table = k_cache_table.data_ptr(), v_cache_table.data_ptr()
+    a.rotary_cos_table = rotary_cos_table.data_ptr() if rotary_cos_table is not None else None
+    a.rotary_sin_table = rotary_sin_table.data_ptr() if rotary_sin_table is not None else None
+    a.lse = lse.data_ptr() if lse is not None else None
+    a.batch_size, a.memory_max_len, a.num_heads, a.head_dim = batch_size, memory_max_len, num_heads, head_dim
+    a.head_dim_inv = 1.0 / math.sqrt(head_dim)                      # src/flash_api.cpp:27
+    a.rotary_embedding_dim = rotary_embedding_dim
+    a.qkv_stride = qkv.stride(0)
+    a.num_layer, a.idx_layer = num_layer, idx_layer
+    a.num_splits = int(num_splits)
+    a.dtype = _dtype_code(qkv)
+    with torch.cuda.device(dev):
+        check(lib.sfa_decoder_step(a, _stream()))
+    return o
+
+
+def compute_rotary_table(max_seq_len: int, rot_embed_dim: int, dtype=torch.float16, device="cuda"):
+    """cos / sin tables of shape (max_seq_len, rot_embed_dim // 2): angle = pos / 10000^(2i/rot_embed_dim)."""
+    cos = torch.empty((max_seq_len, rot_embed_dim // 2), dtype=dtype, device=device)
+    sin = torch.empty_like(cos)
+    with torch.cuda.device(cos.device):
+        check(lib.sfa_rotary_table(cos.data_ptr(), sin.data_ptr(), max_seq_len, rot_embed_dim, _dtype_code(cos), _stream()))
+    return cos, sin
+
+
+def init_half_array(array: torch.Tensor, value: float) -> torch.Tensor:
+    """array[:] = value (the reference's test utility); fp16 or bf16, contiguous."""
+    _require_cuda(array)
+    if not array.is_contiguous():
+        raise ValueError("array must be contiguous")
+    with torch.cuda.device(array.device):
+        check(lib.sfa_fill(array.data_ptr(), float(value), array.numel(), _dtype_code(array), _stream()))
+    return array
+
+
+def fwd_watchdog(clear: bool = True) -> int:
+    """Synchronises and returns the prefill kernel's pipeline watchdog code (0 = healthy)."""
+    rc = lib.sfa_fwd_watchdog(1 if clear else 0)
+    if rc < 0:
+        check(rc)
+    return rc
+
+
+def launch_count() -> int:
+    return int(lib.sfa_launch_count())

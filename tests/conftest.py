@@ -15,3 +15,16 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def built_library():
+    """The C-ABI library is built in-tree (nvcc cross-compiles without a GPU); no fallback exists."""
+    from starflashattention_b200 import build
+    return build.build()
+
+
+def rand_tensor(shape, dtype, seed, scale=1.0):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype)
