@@ -1,0 +1,25 @@
+# Builds build/libStarFlashAttention.so (sm_100a only) and the C++ example, the layout the reference's
+# Makefile produces (reference Makefile:1-36; retargeted, NVTX3 header-only, no cuBLAS).
+PY ?= python
+NVCC ?= nvcc
+ARCH = -gencode arch=compute_100a,code=sm_100a
+PKG_LIB = starflashattention_b200/lib/libStarFlashAttention.so
+
+all: lib example
+
+lib:
+	$(PY) -m starflashattention_b200.build
+	@mkdir -p build
+	@cp -f $(PKG_LIB) build/libStarFlashAttention.so
+
+example: lib
+	$(NVCC) -o build/testFlashDecoder examples/cpp/testFlashDecoder.cc -O2 -std=c++17 $(ARCH) -lineinfo \
+	  -I include -L build -lStarFlashAttention -Xlinker -rpath -Xlinker '$$ORIGIN'
+
+oracle:
+	@echo "the oracle is Python (oracle/naive.py); nothing to compile"
+
+clean:
+	rm -rf build starflashattention_b200/lib
+
+.PHONY: all lib example oracle clean

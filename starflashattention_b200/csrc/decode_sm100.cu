@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
     const int g = p.group;
 
     int len = (p.seqlens ? p.seqlens[b] : p.seqlen_k) + p.seqlen_add;
-    len = len < 0 ? 0 : len;
+    len = max(0, min(len, p.seqlen_k + p.seqlen_add));   // never read past the cache
     // Per-sequence chunking keeps ragged batches balanced across the splits.
     const int chunk = (((len + p.num_splits - 1) / p.num_splits) + 63) & ~63;
     const int k_begin = split * chunk;

@@ -1,0 +1,155 @@
+"""GPU parity: the tcgen05/TMA prefill forward, through the C ABI, against the CPU oracle
+(softmax(QK^T/sqrt(d))V of the reference's Python example, examples/python/testFlashDecoder.py:84-92).
+
+Tolerances (north_star): |O - O_oracle| <= 2e-3 (fp16); bf16 adds its own output rounding (rtol 4e-3);
+LSE within 1e-3.  The oracle runs in fp32 on the same fp16/bf16-rounded inputs.
+"""
+import pytest
+import torch
+
+from oracle import naive
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, dtype, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype)
+
+
+def _check(o, lse, o_ref, lse_ref, dtype, what=""):
+    atol, rtol = (2e-3, 0.0) if dtype == torch.float16 else (2e-3, 4e-3)
+    err = (o.float().cpu() - o_ref.float()).abs()
+    bound = atol + rtol * o_ref.float().abs()
+    assert bool((err <= bound).all()), f"{what} O: max err {float(err.max()):.3e}"
+    lse = lse.cpu()
+    fin = torch.isfinite(lse_ref)
+    assert torch.equal(torch.isfinite(lse), fin), f"{what} LSE finiteness"
+    if fin.any():
+        assert float((lse[fin] - lse_ref[fin]).abs().max()) <= 1e-3, f"{what} LSE"
+
+
+@pytest.fixture(autouse=True)
+def _watchdog():
+    import starflashattention_b200 as sfa
+    yield
+    assert sfa.fwd_watchdog(clear=True) == 0, "prefill pipeline watchdog fired (an mbarrier wait timed out)"
+
+
+CASES = [
+    # B, Sq, Sk, Hq, Hkv, D, causal
+    (1, 128, 128, 1, 1, 128, False),      # one tile
+    (1, 128, 128, 1, 1, 128, True),
+    (1, 256, 256, 2, 2, 128, False),      # two query tiles in one CTA
+    (2, 512, 512, 4, 2, 128, True),       # GQA, several key tiles
+    (1, 200, 333, 2, 1, 128, False),      # ragged tails on both axes
+    (1, 333, 333, 2, 2, 128, True),
+    (1, 100, 419, 2, 2, 128, True),       # Sq < Sk, bottom-right aligned mask
+    (1, 300, 140, 1, 1, 128, True),       # Sq > Sk: leading rows see no key (O = 0, LSE = -inf)
+    (1, 1, 257, 4, 4, 128, False),        # single query row
+    (2, 384, 384, 2, 2, 64, False),       # head_dim 64
+    (1, 640, 640, 4, 1, 64, True),
+    (1, 1024, 1024, 8, 8, 128, True),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("B,Sq,Sk,Hq,Hkv,D,causal", CASES)
+def test_fwd_matches_oracle(dtype, B, Sq, Sk, Hq, Hkv, D, causal):
+    import starflashattention_b200 as sfa
+    q = _rand((B, Sq, Hq, D), dtype, 1)
+    k = _rand((B, Sk, Hkv, D), dtype, 2)
+    v = _rand((B, Sk, Hkv, D), dtype, 3)
+    o_ref, lse_ref = naive.attention_fwd(q, k, v, causal=causal)
+    o, lse = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=causal)
+    torch.cuda.synchronize()
+    _check(o, lse, o_ref, lse_ref, dtype)
+
+
+def test_fwd_c1_shape_against_fp32_reference():
+    """BASELINE config 1 (B=1 H=8 N=512 d=64): the repo's naive fp32 check, run in fp16 on the GPU."""
+    import starflashattention_b200 as sfa
+    q, k, v = (_rand((1, 512, 8, 64), torch.float16, s) for s in (5, 6, 7))
+    o_ref, lse_ref = naive.attention_fwd(q, k, v)
+    o, lse = sfa.fwd(q.cuda(), k.cuda(), v.cuda())
+    _check(o, lse, o_ref, lse_ref, torch.float16, "C1")
+
+
+def test_fwd_strided_views_and_scale():
+    """q/k/v sliced out of a packed (B, S, 3, H, D) tensor, non-default softmax scale."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    qkv = _rand((2, 300, 3, 4, 128), dtype, 9)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    o_ref, lse_ref = naive.attention_fwd(q, k, v, causal=True, softmax_scale=0.05)
+    d = qkv.cuda()
+    o, lse = sfa.fwd(d[:, :, 0], d[:, :, 1], d[:, :, 2], causal=True, softmax_scale=0.05)
+    _check(o, lse, o_ref, lse_ref, dtype, "strided")
+
+
+def test_fwd_outlier_scores():
+    """A +30 outlier late in the sequence forces the lazy O rescale; heavy-tailed inputs."""
+    import starflashattention_b200 as sfa
+    dtype = torch.float16
+    q = _rand((1, 384, 2, 128), dtype, 13)
+    k = _rand((1, 384, 2, 128), dtype, 14)
+    v = _rand((1, 384, 2, 128), dtype, 15)
+    k[0, 300, 0] = q[0, 17, 0] * 3.0
+    k[0, 10, 1] = q[0, 200, 1] * 2.5
+    o_ref, lse_ref = naive.attention_fwd(q, k, v)
+    o, lse = sfa.fwd(q.cuda(), k.cuda(), v.cuda())
+    assert torch.isfinite(o).all()
+    _check(o, lse, o_ref, lse_ref, dtype, "outlier")
+
+
+def test_fwd_causal_prefix_property():
+    """Size-independent property: under the causal mask, row i depends on keys <= i only, so the first n
+    rows of a long run equal a run on the n-row prefix."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    q, k, v = (_rand((1, 2048, 2, 128), dtype, s).cuda() for s in (21, 22, 23))
+    o_full, lse_full = sfa.fwd(q, k, v, causal=True)
+    n = 768
+    o_pre, lse_pre = sfa.fwd(q[:, :n], k[:, :n], v[:, :n], causal=True)
+    assert float((o_full[:, :n].float() - o_pre.float()).abs().max()) <= 2e-3
+    assert float((lse_full[:, :, :n] - lse_pre).abs().max()) <= 1e-4
+
+
+def _spot_check(q, k, v, o, lse, causal, rows, heads, dtype):
+    """Oracle on sampled (batch, head) slices and query rows of a large problem."""
+    g = q.shape[2] // k.shape[2]
+    Sq, Sk = q.shape[1], k.shape[1]
+    for (b, h) in heads:
+        qs = q[b:b + 1, rows, h:h + 1].cpu()
+        ks, vs = k[b:b + 1, :, h // g:h // g + 1].cpu(), v[b:b + 1, :, h // g:h // g + 1].cpu()
+        for i, r in enumerate(rows):
+            lim = r + (Sk - Sq) + 1 if causal else Sk
+            o_ref, lse_ref = naive.attention_fwd(qs[:, i:i + 1], ks[:, :lim], vs[:, :lim])
+            _check(o[b:b + 1, r:r + 1, h:h + 1], lse[b:b + 1, h:h + 1, r:r + 1], o_ref, lse_ref, dtype, f"b{b} h{h} r{r}")
+
+
+def test_fwd_full_c3_shape_spot_check():
+    """BASELINE config 3 at full size (causal bf16 B=8 H=32 N=8192 d=128): sampled rows of sampled heads
+    against the oracle, everything for finiteness."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    B, S, H, D = 8, 8192, 32, 128
+    g = torch.Generator(device="cuda").manual_seed(3)
+    q, k, v = (torch.randn((B, S, H, D), generator=g, device="cuda", dtype=torch.float32).to(dtype) for _ in range(3))
+    o, lse = sfa.fwd(q, k, v, causal=True)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o).all() and torch.isfinite(lse).all()
+    _spot_check(q, k, v, o, lse, True, [0, 127, 128, 4095, 4096, 8191], [(0, 0), (7, 31), (3, 17)], dtype)
+
+
+def test_fwd_full_c2_shape_spot_check():
+    """BASELINE config 2 at full size (non-causal fp16 B=4 H=16 N=4096 d=64)."""
+    import starflashattention_b200 as sfa
+    dtype = torch.float16
+    B, S, H, D = 4, 4096, 16, 64
+    g = torch.Generator(device="cuda").manual_seed(2)
+    q, k, v = (torch.randn((B, S, H, D), generator=g, device="cuda", dtype=torch.float32).to(dtype) for _ in range(3))
+    o, lse = sfa.fwd(q, k, v)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o).all() and torch.isfinite(lse).all()
+    _spot_check(q, k, v, o, lse, False, [0, 1000, 4095], [(0, 0), (3, 15)], dtype)
