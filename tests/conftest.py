@@ -8,8 +8,18 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+def _build_library():
+    # build.py is loaded by path: importing the package dlopens the library, which may not exist yet
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_sfa_build", os.path.join(ROOT, "starflashattention_b200", "build.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    return b.build()
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    _build_library()
 
 
 @pytest.fixture(scope="session")
@@ -20,8 +30,7 @@ def golden_dir():
 @pytest.fixture(scope="session", autouse=True)
 def built_library():
     """The C-ABI library is built in-tree (nvcc cross-compiles without a GPU); no fallback exists."""
-    from starflashattention_b200 import build
-    return build.build()
+    return _build_library()
 
 
 def rand_tensor(shape, dtype, seed, scale=1.0):
