@@ -75,9 +75,43 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def torch_ext_path() -> str:
+    import sysconfig
+    return os.path.join(ROOT, "star_flash_attn" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_torch_ext(force: bool = False) -> str:
+    """The reference-facing `star_flash_attn` PyTorch extension (csrc/flash_api.cpp, host-only C++) linked against
+    libStarFlashAttention.so.  Written next to the package at the repository root so `import star_flash_attn`
+    works from there, as it does after the reference's `setup.py install` (reference setup.py:9-30)."""
+    import sysconfig
+    from torch.utils import cpp_extension as ce
+    import torch
+    lib = build()
+    out = torch_ext_path()
+    src = os.path.join(CSRC, "flash_api.cpp")
+    if not (force or _stale(out, [src, lib, os.path.join(ROOT, "include", "star_flash_attn.h")])):
+        return out
+    tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    inc = [f"-I{d}" for d in ce.include_paths(device_type="cuda")] + [f"-I{sysconfig.get_paths()['include']}",
+                                                                  f"-I{os.path.join(ROOT, 'include')}"]
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=star_flash_attn",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch.compiled_with_cxx11_abi())}",
+           *inc, src, "-o", out, f"-L{tlib}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
+           "-ltorch_python", f"-L{os.path.dirname(lib)}", "-lStarFlashAttention",
+           f"-Wl,-rpath,{tlib}", "-Wl,-rpath,$ORIGIN/starflashattention_b200/lib"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"star_flash_attn extension build failed:\n{r.stdout}\n{r.stderr}")
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--torch-ext", action="store_true", help="also build the star_flash_attn PyTorch extension")
     a = ap.parse_args()
     print(build(a.force, a.verbose))
+    if a.torch_ext:
+        print(build_torch_ext(a.force))

@@ -25,6 +25,7 @@
 #include <limits.h>
 #include <math.h>
 #include <mutex>
+#include <type_traits>
 
 namespace sfa {
 namespace {
@@ -66,6 +67,69 @@ __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int*
     return true;
 }
 
+// ---- packed fp32x2 arithmetic (FFMA2 / FADD2 / FMUL2 on sm_100): halves the issue slots of the softmax
+__device__ __forceinline__ uint64_t pack_f2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// 2^x for two values on the FMA/ALU pipes instead of the MUFU: x = n + f with n = round(x) taken from the
+// mantissa of x + 1.5*2^23, f in [-0.5, 0.5], 2^f by a degree-3 minimax polynomial (max relative error
+// 7.5e-5, below the bf16/fp16 rounding of P), and n added to the exponent field.  x is clamped at -125
+// so the exponent cannot wrap; callers use this only on tiles without -inf entries.
+__device__ __forceinline__ uint64_t exp2_poly2(float x0, float x1) {
+    constexpr float kMagic = 12582912.f;   // 1.5 * 2^23
+    x0 = fmaxf(x0, -125.f);
+    x1 = fmaxf(x1, -125.f);
+    const uint64_t x = pack_f2(x0, x1);
+    const uint64_t magic = pack_f2(kMagic, kMagic);
+    const uint64_t t = fadd2(x, magic);
+    const uint64_t u = fadd2(t, pack_f2(-kMagic, -kMagic));
+    const uint64_t f = fadd2(x, u ^ 0x8000000080000000ull);   // x - round(x)
+    uint64_t r = ffma2(pack_f2(0.055171459913253784f, 0.055171459913253784f), f,
+                       pack_f2(0.2426108568906784f, 0.2426108568906784f));
+    r = ffma2(r, f, pack_f2(0.6932609677314758f, 0.6932609677314758f));
+    r = ffma2(r, f, pack_f2(0.9999281167984009f, 0.9999281167984009f));
+    float t0, t1, r0, r1;
+    unpack_f2(t, t0, t1);
+    unpack_f2(r, r0, r1);
+    r0 = __int_as_float(__float_as_int(r0) + (__float_as_int(t0) << 23));
+    r1 = __int_as_float(__float_as_int(r1) + (__float_as_int(t1) << 23));
+    return pack_f2(r0, r1);
+}
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
+    if constexpr (BF16) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&v);
+    } else {
+        __half2 v = __floats2half2_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+}
+
+// Register split of the three warpgroups when NQ == 2 (2 x 128 x 224 + 128 x 64 = 65536).
+constexpr int kRegsSoftmax = 224;
+constexpr int kRegsOther = 64;
+
 template <int D, int NQ, int NSTAGE>
 struct FwdSmem {
     static constexpr int kSubTileBytes = kBlockM * 128;              // 128 rows x 64 elements x 2 B
@@ -80,7 +144,9 @@ struct FwdSmem {
     static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
 };
 
-template <int D, int NQ, int NSTAGE>
+// BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
+// DBG: 0 = product; 1..3 = timing probes that give wrong results (see tools/fwd_probe.py).
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
 __global__ void __launch_bounds__(NQ == 2 ? 384 : 192, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const FwdParams p) {
@@ -157,7 +223,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     // warps) so the register file can be re-split: the softmax warpgroups take what the others give up.
     if (warp == kSoftmaxWarps) {
         // =============================================================== TMA producer
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
         if (lane == 0) {
 #pragma unroll
             for (int q = 0; q < NQ; ++q) {
@@ -181,10 +247,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
     } else if (warp == kSoftmaxWarps + 1) {
         // =============================================================== tcgen05 issuer
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
         if (lane == 0) {
-            const uint32_t idesc_qk = mma_idesc(p.is_bf16, 0, 0, kBlockM, kBlockN);
-            const uint32_t idesc_pv = mma_idesc(p.is_bf16, 0, 1, kBlockM, D);
+            const uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
+            const uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
             // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
             // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
             constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
@@ -252,7 +318,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
     } else if (warp < kSoftmaxWarps) {
         // =============================================================== softmax warpgroups
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSoftmax));
         const int q = warp >> 2;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const int row = m0 + q * kBlockM + row_in_tile;
@@ -262,43 +328,70 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         const int n_q = n_tiles[q];
         const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
         const float sl2 = p.scale_log2;
+        const uint64_t sl2_2 = pack_f2(sl2, sl2);
 
         float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
-        float l_sum = 0.f;
+        uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
         bool ok = true;
 
         for (int j = 0; j < n_q && ok; ++j) {
             ok = wait_barrier(bar_s_full(q), j & 1, p.error_flag, 7);
             tc_fence_after();
+            if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
+                tc_fence_before();
+                mbar_arrive(bar_p_ready(q));
+                continue;
+            }
             uint32_t su[kBlockN];
-#pragma unroll
-            for (int c = 0; c < kBlockN / 32; ++c) tmem_ld32(s_tmem + 32 * c, &su[32 * c]);
+            tmem_ld32(s_tmem, &su[0]);
+            tmem_ld32(s_tmem + 32, &su[32]);
             tmem_wait_ld();
-            float s[kBlockN];
+            tmem_ld32(s_tmem + 64, &su[64]);
+            tmem_ld32(s_tmem + 96, &su[96]);
+            if constexpr (DBG == 3) {      // TMEM traffic probe: load S, store raw halves back as P
+                tmem_wait_ld();
+                uint32_t pk[kBlockN / 2];
 #pragma unroll
-            for (int c = 0; c < kBlockN; ++c) s[c] = __uint_as_float(su[c]);
+                for (int c = 0; c < kBlockN / 2; ++c) pk[c] = __byte_perm(su[2 * c], su[2 * c + 1], 0x7632);
+                tmem_st32(s_tmem, &pk[0]);
+                tmem_st32(s_tmem + 32, &pk[32]);
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(bar_p_ready(q));
+                continue;
+            }
 
             const int key0 = j * kBlockN;
             const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
                                    (key0 + kBlockN > p.seqlen_k);
-            if (need_mask) {
-                const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay
+            const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
+            // ---- row maximum: four independent chains, first half while the second half is in flight
+            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            auto scan_half = [&](int base) {
+                if (need_mask) {
 #pragma unroll
-                for (int c = 0; c < kBlockN; ++c)
-                    if (c > lim) s[c] = -INFINITY;
-            }
-            float mx = s[0];
+                    for (int c = base; c < base + kBlockN / 2; ++c)
+                        if (c > lim) su[c] = 0xff800000u;   // -inf
+                }
 #pragma unroll
-            for (int c = 1; c < kBlockN; ++c) mx = fmaxf(mx, s[c]);
+                for (int c = base; c < base + kBlockN / 2; c += 2)
+                    mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
+            };
+            scan_half(0);
+            tmem_wait_ld();
+            scan_half(kBlockN / 2);
+            const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
 
-            const float m_new = fmaxf(m_used, mx);
+            const float m_new = fmaxf(m_used, mx_all);
             if (j == 0) {
                 m_used = m_new;
             } else {
                 const bool grow = (m_new - m_used) * sl2 > kRescaleThreshold;   // false for -inf - -inf (NaN)
                 if (__any_sync(0xffffffffu, grow)) {
                     const float alpha = grow ? ex2((m_used - m_new) * sl2) : 1.f;
-                    l_sum *= alpha;
+                    const uint64_t alpha2 = pack_f2(alpha, alpha);
+                    l_acc[0] = fmul2(l_acc[0], alpha2);
+                    l_acc[1] = fmul2(l_acc[1], alpha2);
                     if (grow) m_used = m_new;
 #pragma unroll
                     for (int c = 0; c < D / 32; ++c) {
@@ -312,28 +405,46 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 }
             }
             const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
-            uint32_t pk[kBlockN / 2];
+            const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
+            // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
+            // pairs on tiles without masked (-inf) entries; P leaves for TMEM in two halves of 64 keys.
+            auto exp_and_store = [&](auto poly_tag) {
+                constexpr int kPoly = decltype(poly_tag)::value;
 #pragma unroll
-            for (int c = 0; c < kBlockN; c += 2) {
-                const float p0 = ex2(fmaf(s[c], sl2, neg_m));
-                const float p1 = ex2(fmaf(s[c + 1], sl2, neg_m));
-                l_sum += p0 + p1;
-                if (p.is_bf16) {
-                    __nv_bfloat162 v = __floats2bfloat162_rn(p0, p1);
-                    pk[c / 2] = *reinterpret_cast<uint32_t*>(&v);
-                } else {
-                    __half2 v = __floats2half2_rn(p0, p1);
-                    pk[c / 2] = *reinterpret_cast<uint32_t*>(&v);
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t pk[kBlockN / 4];
+#pragma unroll
+                    for (int i = 0; i < kBlockN / 4; ++i) {
+                        const int c = half * (kBlockN / 2) + 2 * i;
+                        const uint64_t x2 =
+                            ffma2(pack_f2(__uint_as_float(su[c]), __uint_as_float(su[c + 1])), sl2_2, neg_m2);
+                        float x0, x1, p0, p1;
+                        unpack_f2(x2, x0, x1);
+                        if constexpr (DBG == 1) {
+                            p0 = x0; p1 = x1;
+                        } else if ((i & 7) >= 8 - kPoly) {
+                            unpack_f2(exp2_poly2(x0, x1), p0, p1);
+                        } else {
+                            p0 = ex2(x0); p1 = ex2(x1);
+                        }
+                        l_acc[i & 1] = fadd2(l_acc[i & 1], pack_f2(p0, p1));
+                        pk[i] = pack_pair<BF16>(p0, p1);
+                    }
+                    tmem_st32(s_tmem + 32 * half, pk);
                 }
-            }
-#pragma unroll
-            for (int c = 0; c < kBlockN / 64; ++c) tmem_st32(s_tmem + 32 * c, &pk[32 * c]);
+            };
+            if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
+            else exp_and_store(std::integral_constant<int, 0>{});
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(bar_p_ready(q));
         }
 
         // ---- epilogue: O / l -> global, LSE
+        float l0, l1, l2, l3;
+        unpack_f2(l_acc[0], l0, l1);
+        unpack_f2(l_acc[1], l2, l3);
+        const float l_sum = (l0 + l1) + (l2 + l3);
         const bool row_ok = row < p.seqlen_q;
         const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
         uint8_t* o_row = reinterpret_cast<uint8_t*>(p.o) +
@@ -352,16 +463,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             }
             uint32_t packed[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const float a = __uint_as_float(o[2 * i]) * inv_l, c2 = __uint_as_float(o[2 * i + 1]) * inv_l;
-                if (p.is_bf16) {
-                    __nv_bfloat162 v = __floats2bfloat162_rn(a, c2);
-                    packed[i] = *reinterpret_cast<uint32_t*>(&v);
-                } else {
-                    __half2 v = __floats2half2_rn(a, c2);
-                    packed[i] = *reinterpret_cast<uint32_t*>(&v);
-                }
-            }
+            for (int i = 0; i < 16; ++i)
+                packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
             if (row_ok) {
                 uint4* dst = reinterpret_cast<uint4*>(o_row + 64 * c);
 #pragma unroll
@@ -376,7 +479,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     }
 
     else {
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");   // idle warps of the third warpgroup
+        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));   // idle warps of the third warpgroup
     }
 
     // ---- teardown: every tcgen05 operation of this CTA has completed once the softmax warps are here
@@ -425,11 +528,11 @@ int make_map(CUtensorMap* map, const void* base, int dtype, int head_dim, int he
     return SFA_OK;
 }
 
-template <int D, int NQ, int NSTAGE>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
 int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p,
                     int batch, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -442,6 +545,37 @@ int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensor
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return SFA_OK;
+}
+
+// Host launcher: the tile configuration per (head_dim, rows, dtype).  kPolyDefault of every 8 column pairs
+// take the polynomial exp2 (the MUFU is co-critical with the tensor pipe at head_dim 128 and dominant at 64).
+constexpr int kPolyDefault128 = 2;
+constexpr int kPolyDefault64 = 3;
+
+template <bool BF16>
+int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p, int batch,
+                 int head_dim, int nq, cudaStream_t stream) {
+    // Tuning / probe overrides (tools/fwd_probe.py): SFA_FWD_POLY in {0,2,3,4}, SFA_FWD_DBG in {1,2,3}; bf16 d=128 NQ=2 only.
+    static const int poly = [] { const char* e = getenv("SFA_FWD_POLY"); return e ? atoi(e) : -1; }();
+    static const int dbg = [] { const char* e = getenv("SFA_FWD_DBG"); return e ? atoi(e) : 0; }();
+    if (head_dim == 128) {
+        if (nq == 1) return launch_instance<128, 1, 4, BF16, kPolyDefault128, 0>(qm, km, vm, p, batch, stream);
+        if constexpr (BF16) {
+            if (dbg == 1) return launch_instance<128, 2, 4, true, 0, 1>(qm, km, vm, p, batch, stream);
+            if (dbg == 2) return launch_instance<128, 2, 4, true, 0, 2>(qm, km, vm, p, batch, stream);
+            if (dbg == 3) return launch_instance<128, 2, 4, true, 0, 3>(qm, km, vm, p, batch, stream);
+            if (poly == 0) return launch_instance<128, 2, 4, true, 0, 0>(qm, km, vm, p, batch, stream);
+            if (poly == 3) return launch_instance<128, 2, 4, true, 3, 0>(qm, km, vm, p, batch, stream);
+            if (poly == 4) return launch_instance<128, 2, 4, true, 4, 0>(qm, km, vm, p, batch, stream);
+        }
+        return launch_instance<128, 2, 4, BF16, kPolyDefault128, 0>(qm, km, vm, p, batch, stream);
+    }
+    if (nq == 1) return launch_instance<64, 1, 6, BF16, kPolyDefault64, 0>(qm, km, vm, p, batch, stream);
+    if constexpr (!BF16) {
+        if (poly == 0) return launch_instance<64, 2, 6, false, 0, 0>(qm, km, vm, p, batch, stream);
+        if (poly == 4) return launch_instance<64, 2, 6, false, 4, 0>(qm, km, vm, p, batch, stream);
+    }
+    return launch_instance<64, 2, 6, BF16, kPolyDefault64, 0>(qm, km, vm, p, batch, stream);
 }
 
 }  // namespace
@@ -496,11 +630,8 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
 
     static int forced_nq = [] { const char* e = getenv("SFA_FWD_NQ"); return e ? atoi(e) : 0; }();
     const int nq = forced_nq == 1 || forced_nq == 2 ? forced_nq : (a.seqlen_q > kBlockM ? 2 : 1);
-    if (a.head_dim == 128)
-        return nq == 2 ? launch_instance<128, 2, 4>(qm, km, vm, p, a.batch, stream)
-                       : launch_instance<128, 1, 4>(qm, km, vm, p, a.batch, stream);
-    return nq == 2 ? launch_instance<64, 2, 6>(qm, km, vm, p, a.batch, stream)
-                   : launch_instance<64, 1, 6>(qm, km, vm, p, a.batch, stream);
+    return a.dtype == SFA_BF16 ? launch_dtype<true>(qm, km, vm, p, a.batch, a.head_dim, nq, stream)
+                               : launch_dtype<false>(qm, km, vm, p, a.batch, a.head_dim, nq, stream);
 }
 
 }  // namespace sfa

@@ -17,6 +17,14 @@ def _build_library():
     return b.build()
 
 
+def _build_torch_ext():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_sfa_build", os.path.join(ROOT, "starflashattention_b200", "build.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    return b.build_torch_ext()
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
     _build_library()
@@ -31,6 +39,14 @@ def golden_dir():
 def built_library():
     """The C-ABI library is built in-tree (nvcc cross-compiles without a GPU); no fallback exists."""
     return _build_library()
+
+
+@pytest.fixture(scope="session")
+def torch_ext(built_library):
+    """The reference-facing `star_flash_attn` extension module (host-only C++ over the C ABI), built in-tree."""
+    _build_torch_ext()
+    import star_flash_attn
+    return star_flash_attn
 
 
 def rand_tensor(shape, dtype, seed, scale=1.0):

@@ -89,3 +89,16 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("the oracle", ""), os.path.join(dirpath, f)
+
+
+def test_torch_extension_keeps_the_reference_signature(torch_ext):
+    """`star_flash_attn.mha_fwd_cuda` takes the reference's 16 keyword arguments (src/flash_api.cpp:74-79)."""
+    doc = torch_ext.mha_fwd_cuda.__doc__
+    names = ["qkv", "q_bias", "k_bias", "v_bias", "k_cache_table", "v_cache_table", "seq_len", "o", "batch_size",
+             "memory_max_len", "num_heads", "head_dim", "rotary_embedding_dim", "max_input_length", "num_layer", "idx_layer"]
+    pos = [doc.index(n + ":") for n in names]
+    assert pos == sorted(pos)
+    assert hasattr(torch_ext, "fwd") and hasattr(torch_ext, "decode")
+    t = torch.zeros(1, 3, 1, 128, dtype=torch.float16)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        torch_ext.mha_fwd_cuda(t, t, t, t, t, t, torch.zeros(1, dtype=torch.int32), t, 1, 8, 1, 128, 128, 8, 1, 0)

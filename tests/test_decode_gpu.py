@@ -237,3 +237,44 @@ def test_all_ones_fixture_of_the_cpp_example():
         sfa.mha_fwd_cuda(qkv, None, None, None, kc, vc, seq, o, B, M, H, D, D, M, L, 0,
                          rotary_cos_table=cos, rotary_sin_table=sin)
         assert float((o.float() - 1.0).abs().max()) <= 1e-3
+
+
+def test_torch_extension_decoder_step_matches_oracle(torch_ext):
+    """The pybind entry the reference's Python example calls (examples/python/testFlashDecoder.py:124-126)."""
+    B, L, M, H, D = 2, 3, 640, 8, 128
+    g = torch.Generator().manual_seed(77)
+    qkv = torch.randn(B, 3, H, D, generator=g).half()
+    kt = torch.randn(B, L, M, H, D, generator=g).half()
+    vt = torch.randn(B, L, M, H, D, generator=g).half()
+    seq = torch.tensor([511, 130], dtype=torch.int32)
+    o_ref, _, _, _ = naive.decode_step_reference(qkv, kt, vt, seq, 2)
+    o = torch.empty(B, H, D, dtype=torch.float16, device="cuda")
+    bias = torch.empty(0, device="cuda")
+    n0 = torch_ext.launch_count()
+    ret = torch_ext.mha_fwd_cuda(qkv=qkv.cuda(), q_bias=bias, k_bias=bias, v_bias=bias, k_cache_table=kt.cuda(),
+                                 v_cache_table=vt.cuda(), seq_len=seq.cuda(), o=o, batch_size=B, memory_max_len=M,
+                                 num_heads=H, head_dim=D, rotary_embedding_dim=D, max_input_length=M, num_layer=L,
+                                 idx_layer=2)
+    torch.cuda.synchronize()
+    assert ret.data_ptr() == o.data_ptr()
+    assert torch_ext.launch_count() > n0
+    assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 3e-3
+
+
+def test_torch_extension_fwd_and_decode(torch_ext):
+    g = torch.Generator().manual_seed(78)
+    q = torch.randn(1, 300, 4, 128, generator=g).half()
+    k = torch.randn(1, 300, 2, 128, generator=g).half()
+    v = torch.randn(1, 300, 2, 128, generator=g).half()
+    o_ref, lse_ref = naive.attention_fwd(q, k, v, causal=True)
+    o, lse = torch_ext.fwd(q.cuda(), k.cuda(), v.cuda(), causal=True)
+    assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 2e-3
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+    qd = torch.randn(2, 8, 128, generator=g).half()
+    kc = torch.randn(2, 1000, 2, 128, generator=g).half()
+    vc = torch.randn(2, 1000, 2, 128, generator=g).half()
+    sl = torch.tensor([1000, 17], dtype=torch.int32)
+    o_ref, lse_ref = naive.decode_attention(qd, kc, vc, sl)
+    o, lse = torch_ext.decode(qd.cuda(), kc.cuda(), vc.cuda(), sl.cuda())
+    assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 2e-3
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3

@@ -1,0 +1,46 @@
+"""Device-resident timing of the prefill kernel for one configuration (env overrides SFA_FWD_POLY / SFA_FWD_DBG
+are read by the library at first launch, so every variant runs in its own process).
+
+    python tools/fwd_time.py c3|c2|c5 [iters]
+"""
+import os
+import statistics
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import starflashattention_b200 as sfa  # noqa: E402
+
+CFG = {"c3": (torch.bfloat16, 8, 32, 8192, 128, True), "c2": (torch.float16, 4, 16, 4096, 64, False),
+       "c5": (torch.bfloat16, 1, 32, 65536, 128, True), "c3nc": (torch.bfloat16, 8, 32, 8192, 128, False),
+       "c2b": (torch.float16, 16, 16, 4096, 64, False)}
+
+
+def main():
+    name = sys.argv[1] if len(sys.argv) > 1 else "c3"
+    iters = int(sys.argv[2]) if len(sys.argv) > 2 else 10
+    dt, B, H, S, D, causal = CFG[name]
+    g = torch.Generator(device="cuda").manual_seed(0)
+    q, k, v = (torch.randn((B, S, H, D), generator=g, device="cuda", dtype=torch.float32).to(dt) for _ in range(3))
+    out = torch.empty_like(q)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(3):
+        sfa.fwd(q, k, v, causal=causal, out=out)
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); sfa.fwd(q, k, v, causal=causal, out=out); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ms = statistics.median(ts)
+    flops = 4.0 * B * H * S * S * D * (0.5 if causal else 1.0)
+    wd = sfa.fwd_watchdog()
+    print(f"[fwd_time] {name} POLY={os.environ.get('SFA_FWD_POLY','-')} DBG={os.environ.get('SFA_FWD_DBG','-')} "
+          f"median {ms:.3f} ms  min {min(ts):.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s (median)  watchdog={wd}", flush=True)
+
+
+if __name__ == "__main__":
+    main()
