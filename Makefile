@@ -8,7 +8,7 @@ PKG_LIB = starflashattention_b200/lib/libStarFlashAttention.so
 all: lib example
 
 lib:
-	$(PY) -m starflashattention_b200.build
+	$(PY) starflashattention_b200/build.py
 	@mkdir -p build
 	@cp -f $(PKG_LIB) build/libStarFlashAttention.so
 

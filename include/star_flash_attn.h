@@ -143,6 +143,9 @@ uint64_t sfa_launch_count(void);
  * out ends the kernel and latches a non-zero code here.  Synchronises the device; returns the code
  * (0 = healthy) or a negative sfa_status, and clears the latch when `clear` is non-zero. */
 int sfa_fwd_watchdog(int clear);
+/* Tuning aid: cycle counters written by the instrumented prefill build (SFA_FWD_DBG=5, tools/fwd_probe.py);
+ * copies min(n, 32) 64-bit counters after synchronising the device. */
+int sfa_fwd_probe_read(uint64_t* out, int32_t n);
 /* Releases the per-device workspaces (synchronises the device). */
 void sfa_release_workspaces(void);
 

@@ -1,11 +1,11 @@
 """B200-native (sm_100a) FlashAttention forward and split-KV decode behind the StarFlashAttention interface.
 
 Importing the package loads ``lib/libStarFlashAttention.so`` through its C ABI; there is no CPU or
-PyTorch fallback, so a missing library is an ImportError (build with ``python -m starflashattention_b200.build``).
+PyTorch fallback, so a missing library is an ImportError (build with ``python starflashattention_b200/build.py``).
 """
-from .interface import (compute_rotary_table, decode, decode_num_splits, fwd, fwd_watchdog, init_half_array,
-                        launch_count, mha_fwd_cuda)
+from .interface import (compute_rotary_table, decode, decode_host, decode_num_splits, fwd, fwd_host, fwd_watchdog,
+                        init_half_array, launch_count, mha_fwd_cuda)
 from .multi_gpu import partition, shard_batch_heads
 
-__all__ = ["fwd", "decode", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
+__all__ = ["fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
            "launch_count", "decode_num_splits", "partition", "shard_batch_heads"]

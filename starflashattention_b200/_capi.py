@@ -1,7 +1,7 @@
 """ctypes binding of libStarFlashAttention.so (the C ABI declared in include/star_flash_attn.h).
 
 There is no CPU fallback: if the shared library has not been built, importing this module raises.
-Build it with ``python -m starflashattention_b200.build`` (or ``__graft_entry__.build()``).
+Build it with ``python starflashattention_b200/build.py`` (or ``__graft_entry__.build()``).
 """
 from __future__ import annotations
 
@@ -18,7 +18,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 EXPORTED_SYMBOLS = (
     "sfa_fwd", "sfa_decode", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
-    "sfa_fwd_watchdog", "sfa_release_workspaces",
+    "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
 )
 # C++-mangled drop-ins of the reference's src/flash_attn.h:7-11.
 MANGLED_DROP_INS = (
@@ -77,7 +77,7 @@ class StarFlashAttentionError(RuntimeError):
 def _load() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            f"{LIB_PATH} is missing. Build it with `python -m starflashattention_b200.build`; "
+            f"{LIB_PATH} is missing. Build it with `python starflashattention_b200/build.py`; "
             "this package has no CPU or PyTorch fallback.")
     lib = C.CDLL(LIB_PATH)
     lib.sfa_fwd.argtypes = [C.POINTER(FwdArgs), C.c_void_p]
@@ -99,6 +99,8 @@ def _load() -> C.CDLL:
     lib.sfa_launch_count.restype = C.c_uint64
     lib.sfa_fwd_watchdog.argtypes = [C.c_int]
     lib.sfa_fwd_watchdog.restype = C.c_int
+    lib.sfa_fwd_probe_read.argtypes = [C.POINTER(C.c_uint64), C.c_int32]
+    lib.sfa_fwd_probe_read.restype = C.c_int
     lib.sfa_release_workspaces.restype = None
     return lib
 

@@ -1,6 +1,6 @@
 """Build recipe of libStarFlashAttention.so (nvcc, sm_100a only, in-tree output).
 
-    python -m starflashattention_b200.build [--force] [--verbose]
+    python starflashattention_b200/build.py [--force] [--verbose]
 
 The library is written to ``starflashattention_b200/lib/libStarFlashAttention.so`` so that it travels
 with the repository snapshot to the GPU box.  nvcc cross-compiles without a GPU.

@@ -162,6 +162,12 @@ int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream) {
     return sfa::launch_fill(array, value, n, dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int sfa_fwd_probe_read(uint64_t* out, int32_t n) {
+    if (!out || n <= 0) return sfa::fail(SFA_ERR_INVALID, "sfa_fwd_probe_read: null buffer");
+    if (cudaDeviceSynchronize() != cudaSuccess) return sfa::fail(SFA_ERR_CUDA, "device synchronize failed");
+    return sfa::fwd_probe_read(reinterpret_cast<unsigned long long*>(out), n);
+}
+
 int sfa_fwd_watchdog(int clear) {
     if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
     cudaError_t e = cudaDeviceSynchronize();

@@ -48,7 +48,8 @@ struct FwdParams {
     float scale_log2;
 };
 
-__device__ int g_fwd_error;   // set when an mbarrier wait times out (pipeline bug guard)
+__device__ int g_fwd_error;
+__device__ unsigned long long g_fwd_probe[32];   // DBG == 5: cycle counters of CTA (0,0,0), see tools/fwd_probe.py   // set when an mbarrier wait times out (pipeline bug guard)
 
 // Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.
 __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
@@ -126,9 +127,14 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
     }
 }
 
-// Register split of the three warpgroups when NQ == 2 (2 x 128 x 224 + 128 x 64 = 65536).
-constexpr int kRegsSoftmax = 224;
-constexpr int kRegsOther = 64;
+// Register split of the three warpgroups when NQ == 2.  setmaxnreg.inc blocks until the CTA's own pool
+// (registers per thread at launch x 384 threads; 168 under __launch_bounds__(384, 1)) can cover the request, so
+// the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
+constexpr int kRegsLaunch = 168;
+constexpr int kRegsSoftmax = 216;
+constexpr int kRegsOther = 72;
+static_assert(2 * 128 * kRegsSoftmax + 128 * kRegsOther <= 384 * kRegsLaunch, "register split exceeds the CTA pool");
+static_assert(kRegsSoftmax % 8 == 0 && kRegsOther % 8 == 0, "setmaxnreg takes multiples of 8");
 
 template <int D, int NQ, int NSTAGE>
 struct FwdSmem {
@@ -154,6 +160,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     constexpr int kSoftmaxWarps = 4 * NQ;
     constexpr int kTmemCols = (NQ * (kBlockN + D)) <= 256 ? 256 : 512;
     constexpr int kSub = D / 64;
+    constexpr bool kFreeRun = DBG == 4 || DBG == 6 || DBG == 7;   // probes: MMA warp never waits for P
+    constexpr bool kProbe = DBG >= 4;
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -200,7 +208,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         for (int q = 0; q < NQ; ++q) {
             mbar_init(bar_q_full(q), 1);
             mbar_init(bar_s_full(q), 1);
-            mbar_init(bar_p_ready(q), 128);
+            mbar_init(bar_p_ready(q), 4);        // one elected arrival per softmax warp
             mbar_init(bar_o_final(q), 1);
         }
 #pragma unroll
@@ -224,96 +232,140 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     if (warp == kSoftmaxWarps) {
         // =============================================================== TMA producer
         if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
-        if (lane == 0) {
+        // whole warp in the loop (uniform control flow), one elected lane issues
+        {
 #pragma unroll
             for (int q = 0; q < NQ; ++q) {
                 if (n_tiles[q] == 0) continue;
-                mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
 #pragma unroll
-                for (int s = 0; s < kSub; ++s)
-                    tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
-                                64 * s, h, m0 + q * kBlockM, b);
+                    for (int s = 0; s < kSub; ++s)
+                        tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
+                                    64 * s, h, m0 + q * kBlockM, b);
+                }
+                __syncwarp();
             }
             for (int i = 0; i < 2 * n_max; ++i) {
                 const int slot = i % NSTAGE, use = i / NSTAGE;
-                if (!wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1)) break;
-                mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
-                const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+                if (!__all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1))) break;
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
+                    const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
 #pragma unroll
-                for (int s = 0; s < kSub; ++s)
-                    tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
-                                bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
+                    for (int s = 0; s < kSub; ++s)
+                        tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
+                                    bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
+                }
+                __syncwarp();
             }
         }
     } else if (warp == kSoftmaxWarps + 1) {
         // =============================================================== tcgen05 issuer
         if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
-        if (lane == 0) {
-            const uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
-            const uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
+        // The whole warp runs the loop (uniform control flow keeps descriptors in uniform registers); one elected
+        // lane issues.  Descriptors are built once per operand tile and advanced by compile-time constants.
+        {
+            constexpr uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
+            constexpr uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
             // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
             // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
             constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
             constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
+            const uint64_t ring_k_desc = smem_desc_at(desc_kmajor, smem_base + L::kRingOff);
+            const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
+            uint64_t q_desc[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) q_desc[q] = smem_desc_at(desc_kmajor, smem_base + L::kQOff + q * L::kTileBytes);
             bool ok = true;
+            // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
             auto issue_qk = [&](int q, int slot) {
-                const uint32_t q_addr = smem_base + L::kQOff + q * L::kTileBytes;
-                const uint32_t k_addr = smem_base + L::kRingOff + slot * L::kTileBytes;
+                const uint64_t k_desc = ring_k_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
                 const uint32_t s_tmem = tmem_base + q * kBlockN;
 #pragma unroll
                 for (int kc = 0; kc < D / 16; ++kc) {
-                    const uint32_t off = (kc >> 2) * L::kSubTileBytes + (kc & 3) * 32;
-                    mma_ss(s_tmem, smem_desc_at(desc_kmajor, q_addr + off), smem_desc_at(desc_kmajor, k_addr + off),
-                           idesc_qk, kc > 0);
+                    constexpr int dummy = 0; (void)dummy;
+                    const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
+                    mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_qk, kc > 0);
                 }
             };
             auto issue_pv = [&](int q, int slot, bool accumulate) {
-                const uint32_t v_addr = smem_base + L::kRingOff + slot * L::kTileBytes;
+                const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
                 const uint32_t p_tmem = tmem_base + q * kBlockN;
                 const uint32_t o_tmem = tmem_base + NQ * kBlockN + q * D;
 #pragma unroll
                 for (int kc = 0; kc < kBlockN / 16; ++kc)
-                    mma_ts(o_tmem, p_tmem + kc * 8, smem_desc_at(desc_v, v_addr + kc * 2048), idesc_pv,
-                           accumulate || kc > 0);
+                    mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, accumulate || kc > 0);
+            };
+            auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
+                return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
             };
             if (n_max > 0) {
-                ok = wait_barrier(bar_kv_full(0), 0, p.error_flag, 2);
+                ok = wait_all(bar_kv_full(0), 0, 2);
 #pragma unroll
                 for (int q = 0; q < NQ; ++q) {
                     if (!ok || n_tiles[q] == 0) continue;
-                    ok = wait_barrier(bar_q_full(q), 0, p.error_flag, 3);
+                    ok = wait_all(bar_q_full(q), 0, 3);
                     tc_fence_after();
-                    issue_qk(q, 0);
-                    tc_commit(bar_s_full(q));
+                    if (elect_one()) {
+                        issue_qk(q, 0);
+                        tc_commit(bar_s_full(q));
+                    }
+                    __syncwarp();
                 }
-                tc_commit(bar_kv_empty(0));
+                if (elect_one()) tc_commit(bar_kv_empty(0));
+                __syncwarp();
             }
+            long long mt_p[2] = {0, 0}, mt_kv = 0, mt_total = clock64();
             for (int j = 0; j < n_max && ok; ++j) {
                 const int vi = 2 * j + 1, ki = 2 * j + 2;
                 const int vslot = vi % NSTAGE, kslot = ki % NSTAGE;
                 const bool have_next = j + 1 < n_max;
-                ok = wait_barrier(bar_kv_full(vslot), (vi / NSTAGE) & 1, p.error_flag, 4);
+                long long c0 = 0;
+                if constexpr (kProbe) c0 = clock64();
+                ok = wait_all(bar_kv_full(vslot), (vi / NSTAGE) & 1, 4);
+                if constexpr (kProbe) mt_kv += clock64() - c0;
                 bool k_waited = false;
 #pragma unroll
                 for (int q = 0; q < NQ; ++q) {
                     if (ok && j < n_tiles[q]) {
-                        ok = wait_barrier(bar_p_ready(q), j & 1, p.error_flag, 5);
+                        if constexpr (kProbe) c0 = clock64();
+                        if constexpr (!kFreeRun) ok = wait_all(bar_p_ready(q), j & 1, 5);
+                        if constexpr (kProbe) mt_p[q] += clock64() - c0;
                         tc_fence_after();
-                        issue_pv(q, vslot, j > 0);
-                        if (j == n_tiles[q] - 1) tc_commit(bar_o_final(q));
+                        if (elect_one()) {
+                            if constexpr (DBG != 6) issue_pv(q, vslot, j > 0);
+                            if (j == n_tiles[q] - 1) tc_commit(bar_o_final(q));
+                            if (q == NQ - 1) tc_commit(bar_kv_empty(vslot));
+                        }
+                        __syncwarp();
+                    } else if (q == NQ - 1) {
+                        if (elect_one()) tc_commit(bar_kv_empty(vslot));
+                        __syncwarp();
                     }
-                    if (q == NQ - 1) tc_commit(bar_kv_empty(vslot));
                     if (ok && j + 1 < n_tiles[q]) {
                         if (!k_waited) {
-                            ok = wait_barrier(bar_kv_full(kslot), (ki / NSTAGE) & 1, p.error_flag, 6);
+                            if constexpr (kProbe) c0 = clock64();
+                            ok = wait_all(bar_kv_full(kslot), (ki / NSTAGE) & 1, 6);
+                            if constexpr (kProbe) mt_kv += clock64() - c0;
                             tc_fence_after();
                             k_waited = true;
                         }
-                        issue_qk(q, kslot);
-                        tc_commit(bar_s_full(q));
+                        if (elect_one()) {
+                            if constexpr (DBG != 7) issue_qk(q, kslot);
+                            tc_commit(bar_s_full(q));
+                            if (q == NQ - 1 && have_next) tc_commit(bar_kv_empty(kslot));
+                        }
+                        __syncwarp();
+                    } else if (q == NQ - 1 && have_next) {
+                        if (elect_one()) tc_commit(bar_kv_empty(kslot));
+                        __syncwarp();
                     }
-                    if (q == NQ - 1 && have_next) tc_commit(bar_kv_empty(kslot));
                 }
+            }
+            if (kProbe && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+                g_fwd_probe[16] = mt_p[0]; g_fwd_probe[17] = mt_p[NQ - 1]; g_fwd_probe[18] = mt_kv;
+                g_fwd_probe[19] = clock64() - mt_total; g_fwd_probe[20] = n_max;
             }
         }
     } else if (warp < kSoftmaxWarps) {
@@ -334,12 +386,17 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
         bool ok = true;
 
-        for (int j = 0; j < n_q && ok; ++j) {
+        const bool probe = DBG == 5 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
+        long long pt_wait = 0, pt_max = 0, pt_exp = 0, pt0 = 0, pt1 = 0, pt2 = 0;
+        for (int j = 0; j < (kFreeRun ? 0 : n_q) && ok; ++j) {
+            if constexpr (DBG == 5) pt0 = clock64();
             ok = wait_barrier(bar_s_full(q), j & 1, p.error_flag, 7);
             tc_fence_after();
+            if constexpr (DBG == 5) pt1 = clock64();
             if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
                 tc_fence_before();
-                mbar_arrive(bar_p_ready(q));
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_p_ready(q));
                 continue;
             }
             uint32_t su[kBlockN];
@@ -357,7 +414,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 tmem_st32(s_tmem + 32, &pk[32]);
                 tmem_wait_st();
                 tc_fence_before();
-                mbar_arrive(bar_p_ready(q));
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_p_ready(q));
                 continue;
             }
 
@@ -406,6 +464,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             }
             const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
             const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
+            if constexpr (DBG == 5) pt2 = clock64();
             // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
             // pairs on tiles without masked (-inf) entries; P leaves for TMEM in two halves of 64 keys.
             auto exp_and_store = [&](auto poly_tag) {
@@ -437,7 +496,16 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             else exp_and_store(std::integral_constant<int, 0>{});
             tmem_wait_st();
             tc_fence_before();
-            mbar_arrive(bar_p_ready(q));
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_p_ready(q));
+            if constexpr (DBG == 5) {
+                const long long pt3 = clock64();
+                pt_wait += pt1 - pt0; pt_max += pt2 - pt1; pt_exp += pt3 - pt2;
+            }
+        }
+        if (probe) {
+            g_fwd_probe[8 * q + 0] = pt_wait; g_fwd_probe[8 * q + 1] = pt_max; g_fwd_probe[8 * q + 2] = pt_exp;
+            g_fwd_probe[8 * q + 3] = n_q;
         }
 
         // ---- epilogue: O / l -> global, LSE
@@ -564,6 +632,10 @@ int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap
             if (dbg == 1) return launch_instance<128, 2, 4, true, 0, 1>(qm, km, vm, p, batch, stream);
             if (dbg == 2) return launch_instance<128, 2, 4, true, 0, 2>(qm, km, vm, p, batch, stream);
             if (dbg == 3) return launch_instance<128, 2, 4, true, 0, 3>(qm, km, vm, p, batch, stream);
+            if (dbg == 4) return launch_instance<128, 2, 4, true, 0, 4>(qm, km, vm, p, batch, stream);
+            if (dbg == 5) return launch_instance<128, 2, 4, true, 0, 5>(qm, km, vm, p, batch, stream);
+            if (dbg == 6) return launch_instance<128, 2, 4, true, 0, 6>(qm, km, vm, p, batch, stream);
+            if (dbg == 7) return launch_instance<128, 2, 4, true, 0, 7>(qm, km, vm, p, batch, stream);
             if (poly == 0) return launch_instance<128, 2, 4, true, 0, 0>(qm, km, vm, p, batch, stream);
             if (poly == 3) return launch_instance<128, 2, 4, true, 3, 0>(qm, km, vm, p, batch, stream);
             if (poly == 4) return launch_instance<128, 2, 4, true, 4, 0>(qm, km, vm, p, batch, stream);
@@ -582,6 +654,11 @@ int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap
 
 int fwd_error_flag_read(int* value) {
     SFA_CUDA_CHECK(cudaMemcpyFromSymbol(value, g_fwd_error, sizeof(int)));
+    return SFA_OK;
+}
+int fwd_probe_read(unsigned long long* out, int n) {
+    if (n > 32) n = 32;
+    SFA_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_fwd_probe, n * sizeof(unsigned long long)));
     return SFA_OK;
 }
 int fwd_error_flag_clear() {

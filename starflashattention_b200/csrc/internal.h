@@ -70,5 +70,6 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream);
 // Pipeline watchdog of the prefill kernel: non-zero after an mbarrier wait timed out.
 int fwd_error_flag_read(int* value);
 int fwd_error_flag_clear();
+int fwd_probe_read(unsigned long long* out, int n);
 
 }  // namespace sfa

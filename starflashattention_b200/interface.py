@@ -20,7 +20,7 @@ import torch
 from . import _capi
 from ._capi import DecodeArgs, DecoderStepArgs, FwdArgs, check, lib
 
-__all__ = ["fwd", "decode", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
+__all__ = ["fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
            "launch_count", "decode_num_splits"]
 
 
@@ -224,3 +224,173 @@ def fwd_watchdog(clear: bool = True) -> int:
 
 def launch_count() -> int:
     return int(lib.sfa_launch_count())
+
+
+# ------------------------------------------------------------------------------------------------
+# Host-buffer entry points: pinned host tensors in, pinned host tensors out.  The (batch x head) units are
+# independent, so the work is cut into chunks and the host->device copy of chunk i+1, the kernel of chunk i and
+# the device->host copy of chunk i-1 run concurrently on three streams (PCIe is full duplex).
+class _HostPipeline:
+    """Double-buffered device staging for one (shape, dtype, device) signature; cached, grow-never."""
+    _cache = {}
+
+    def __init__(self, dev, shapes_dtypes):
+        self.bufs = [[torch.empty(s, dtype=d, device=dev) for (s, d) in shapes_dtypes] for _ in range(2)]
+        self.s_in = torch.cuda.Stream(device=dev)
+        self.s_out = torch.cuda.Stream(device=dev)
+
+    @classmethod
+    def get(cls, dev, key, shapes_dtypes):
+        k = (dev, key)
+        if k not in cls._cache:
+            if len(cls._cache) >= 8:
+                cls._cache.clear()
+            cls._cache[k] = cls(dev, shapes_dtypes)
+        return cls._cache[k]
+
+
+def _chunk_axis(B: int, H_kv: int, chunks: Optional[int]):
+    """Cut along the batch when it has several entries, else along the kv heads: (axis, count)."""
+    if B > 1:
+        return 0, (min(chunks, B) if chunks else min(B, 8))
+    return 2, (min(chunks, H_kv) if chunks else min(H_kv, 8))
+
+
+def _pinned(t: torch.Tensor, what: str):
+    if t.is_cuda:
+        raise ValueError(f"{what} must be a host tensor (use fwd()/decode() for device tensors)")
+    if not t.is_pinned():
+        raise ValueError(f"{what} must live in pinned host memory (tensor.pin_memory())")
+
+
+def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = False,
+             softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
+             lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
+    """Prefill forward on pinned HOST tensors: q (B,Sq,Hq,D), k/v (B,Sk,Hkv,D) -> (out, lse) in pinned host memory.
+    Asynchronous: the results are complete once the current stream of ``device`` has been synchronised."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _pinned(t, n)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    B, Sq, Hq, D = q.shape
+    _, Sk, Hkv, _ = k.shape
+    if out is None:
+        out = torch.empty(q.shape, dtype=q.dtype, pin_memory=True)
+    if lse is None:
+        lse = torch.empty((B, Hq, Sq), dtype=torch.float32, pin_memory=True)
+    axis, n = _chunk_axis(B, Hkv, chunks)
+    g = Hq // Hkv
+    ext = B if axis == 0 else Hkv
+    step = (ext + n - 1) // n
+    cb, ch = (step, Hkv) if axis == 0 else (B, step)
+    pipe = _HostPipeline.get(dev, ("fwd", q.dtype, cb, Sq, Sk, ch, g, D),
+                             [((cb * Sq * ch * g * D,), q.dtype), ((cb * Sk * ch * D,), k.dtype),
+                              ((cb * Sk * ch * D,), v.dtype), ((cb * Sq * ch * g * D,), q.dtype),
+                              ((cb * ch * g * Sq,), torch.float32)])
+    with torch.cuda.device(dev):
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event(); start.record(cur)
+        pipe.s_in.wait_event(start); pipe.s_out.wait_event(start)
+        ev_comp = [None, None]      # kernel done with staging buffer i (inputs reusable)
+        ev_out = [None, None]       # D2H done with staging buffer i (outputs reusable)
+        for i, lo in enumerate(range(0, ext, step)):
+            hi = min(ext, lo + step)
+            w = hi - lo
+            fq, fk, fv, fo, fl = pipe.bufs[i & 1]
+            if axis == 0:
+                src = (q[lo:hi], k[lo:hi], v[lo:hi]); dst_o, dst_l = out[lo:hi], lse[lo:hi]
+                bs, hq_c, hk_c = w, Hq, Hkv
+            else:
+                src = (q[:, :, lo * g:hi * g], k[:, :, lo:hi], v[:, :, lo:hi])
+                dst_o, dst_l = out[:, :, lo * g:hi * g], lse[:, lo * g:hi * g]
+                bs, hq_c, hk_c = B, w * g, w
+            dq = fq[: bs * Sq * hq_c * D].view(bs, Sq, hq_c, D)
+            dk = fk[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
+            dv = fv[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
+            do = fo[: bs * Sq * hq_c * D].view(bs, Sq, hq_c, D)
+            dl = fl[: bs * hq_c * Sq].view(bs, hq_c, Sq)
+            with torch.cuda.stream(pipe.s_in):
+                if ev_comp[i & 1] is not None:
+                    pipe.s_in.wait_event(ev_comp[i & 1])
+                dq.copy_(src[0], non_blocking=True); dk.copy_(src[1], non_blocking=True); dv.copy_(src[2], non_blocking=True)
+                ev_in = torch.cuda.Event(); ev_in.record(pipe.s_in)
+            cur.wait_event(ev_in)
+            if ev_out[i & 1] is not None:
+                cur.wait_event(ev_out[i & 1])
+            a = FwdArgs()
+            a.q, a.k, a.v, a.o, a.lse = dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), do.data_ptr(), dl.data_ptr()
+            a.batch, a.seqlen_q, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = dq.shape[0], Sq, Sk, dq.shape[2], dk.shape[2], D
+            a.q_batch_stride, a.q_row_stride, a.q_head_stride = dq.stride(0), dq.stride(1), dq.stride(2)
+            a.k_batch_stride, a.k_row_stride, a.k_head_stride = dk.stride(0), dk.stride(1), dk.stride(2)
+            a.v_batch_stride, a.v_row_stride, a.v_head_stride = dv.stride(0), dv.stride(1), dv.stride(2)
+            a.o_batch_stride, a.o_row_stride, a.o_head_stride = do.stride(0), do.stride(1), do.stride(2)
+            a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
+            a.causal, a.dtype = (1 if causal else 0), _dtype_code(q)
+            check(lib.sfa_fwd(a, cur.cuda_stream))
+            ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
+            with torch.cuda.stream(pipe.s_out):
+                pipe.s_out.wait_event(ev_comp[i & 1])
+                dst_o.copy_(do, non_blocking=True); dst_l.copy_(dl, non_blocking=True)
+                ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
+        for e in ev_out:
+            if e is not None:
+                cur.wait_event(e)
+    return out, lse
+
+
+def decode_host(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, seqlens: Optional[torch.Tensor] = None,
+                softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
+                lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
+    """Split-KV decode on pinned HOST tensors: q (B,Hq,D), caches (B,M,Hkv,D), seqlens int32 (B) or None ->
+    (out, lse) in pinned host memory.  The batch is cut into chunks whose cache upload overlaps the previous
+    chunk's kernel and download.  Asynchronous on the current stream of ``device``."""
+    for t, n in ((q, "q"), (k_cache, "k_cache"), (v_cache, "v_cache")):
+        _pinned(t, n)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    B, Hq, D = q.shape
+    _, M, Hkv, _ = k_cache.shape
+    if seqlens is not None:
+        _pinned(seqlens, "seqlens")
+        if seqlens.dtype != torch.int32 or seqlens.numel() != B:
+            raise ValueError("seqlens must be an int32 tensor of shape (batch,)")
+    if out is None:
+        out = torch.empty(q.shape, dtype=q.dtype, pin_memory=True)
+    if lse is None:
+        lse = torch.empty((B, Hq), dtype=torch.float32, pin_memory=True)
+    n = min(chunks, B) if chunks else min(B, 8)
+    step = (B + n - 1) // n
+    pipe = _HostPipeline.get(dev, ("decode", q.dtype, step, M, Hq, Hkv, D),
+                             [((step, Hq, D), q.dtype), ((step, M, Hkv, D), q.dtype), ((step, M, Hkv, D), q.dtype),
+                              ((step,), torch.int32), ((step, Hq, D), q.dtype), ((step, Hq), torch.float32)])
+    with torch.cuda.device(dev):
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event(); start.record(cur)
+        pipe.s_in.wait_event(start); pipe.s_out.wait_event(start)
+        ev_comp, ev_out = [None, None], [None, None]
+        for i, lo in enumerate(range(0, B, step)):
+            hi = min(B, lo + step)
+            w = hi - lo
+            dq, dk, dv, dsl, do, dl = (t[:w] for t in pipe.bufs[i & 1])
+            with torch.cuda.stream(pipe.s_in):
+                if ev_comp[i & 1] is not None:
+                    pipe.s_in.wait_event(ev_comp[i & 1])
+                dq.copy_(q[lo:hi], non_blocking=True)
+                dk.copy_(k_cache[lo:hi], non_blocking=True)
+                dv.copy_(v_cache[lo:hi], non_blocking=True)
+                if seqlens is not None:
+                    dsl.copy_(seqlens[lo:hi], non_blocking=True)
+                ev_in = torch.cuda.Event(); ev_in.record(pipe.s_in)
+            cur.wait_event(ev_in)
+            if ev_out[i & 1] is not None:
+                cur.wait_event(ev_out[i & 1])
+            a = _decode_args(dq, dk, dv, dsl if seqlens is not None else None, do, dl, softmax_scale, 0)
+            check(lib.sfa_decode(a, cur.cuda_stream))
+            ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
+            with torch.cuda.stream(pipe.s_out):
+                pipe.s_out.wait_event(ev_comp[i & 1])
+                out[lo:hi].copy_(do, non_blocking=True)
+                lse[lo:hi].copy_(dl, non_blocking=True)
+                ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
+        for e in ev_out:
+            if e is not None:
+                cur.wait_event(e)
+    return out, lse

@@ -38,8 +38,42 @@ def main():
     ms = statistics.median(ts)
     flops = 4.0 * B * H * S * S * D * (0.5 if causal else 1.0)
     wd = sfa.fwd_watchdog()
+    # sustained loop with NVML clock sampling (what the SM clock does under a seconds-long tensor load)
+    clk = ""
+    try:
+        import threading, time, pynvml as nv
+        nv.nvmlInit(); h = nv.nvmlDeviceGetHandleByIndex(0)
+        stop, sm, pw = threading.Event(), [], []
+        def loop():
+            while not stop.is_set():
+                sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)); pw.append(nv.nvmlDeviceGetPowerUsage(h) / 1e3)
+                time.sleep(0.01)
+        th = threading.Thread(target=loop); th.start()
+        n_sus = max(20, int(1000 / ms))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_sus):
+            sfa.fwd(q, k, v, causal=causal, out=out)
+        e1.record(); torch.cuda.synchronize()
+        stop.set(); th.join()
+        half = sm[len(sm) // 2:]
+        clk = (f" | sustained x{n_sus}: {e0.elapsed_time(e1) / n_sus:.3f} ms/iter, SM clock median(2nd half) "
+               f"{statistics.median(half):.0f} MHz min {min(sm)} max {max(sm)}, power max {max(pw):.0f} W")
+    except Exception as e:  # noqa: BLE001
+        clk = f" | clock sampling failed: {e!r}"
+    if os.environ.get("SFA_FWD_DBG") in ("4", "5", "6", "7"):
+        import ctypes
+        from starflashattention_b200 import _capi
+        buf = (ctypes.c_uint64 * 32)()
+        _capi.lib.sfa_fwd_probe_read(buf, 32)
+        v_ = list(buf)
+        for qq in (0, 1):
+            n = max(1, v_[8 * qq + 3])
+            print(f"[probe] softmax q{qq}: tiles {n}  per tile: wait S {v_[8*qq]/n:.0f}  ld+max {v_[8*qq+1]/n:.0f}  exp+store {v_[8*qq+2]/n:.0f} cycles")
+        n = max(1, v_[20])
+        print(f"[probe] mma warp: iters {n}  per iter: wait P0 {v_[16]/n:.0f}  wait P1 {v_[17]/n:.0f}  wait KV {v_[18]/n:.0f}  total {v_[19]/n:.0f} cycles")
     print(f"[fwd_time] {name} POLY={os.environ.get('SFA_FWD_POLY','-')} DBG={os.environ.get('SFA_FWD_DBG','-')} "
-          f"median {ms:.3f} ms  min {min(ts):.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s (median)  watchdog={wd}", flush=True)
+          f"median {ms:.3f} ms  min {min(ts):.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s (median)  watchdog={wd}{clk}", flush=True)
 
 
 if __name__ == "__main__":
