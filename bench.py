@@ -236,27 +236,29 @@ def run_ours(args):
     ms_per_step = ms_max / args.steps
     value = world * units["amount"] / (ms_per_step / 1e3)
 
-    # ---- end to end: pinned host inputs -> H2D -> kernel -> D2H of the result, every step
-    lse_host = None
+    # ---- end to end through the public host-buffer API (fwd_host / decode_host): pinned host inputs -> H2D ->
+    # kernel -> D2H of the result, every step; the API cuts the independent (batch x head) units into chunks so
+    # that upload, kernel and download overlap on three streams.
     out_host = torch.empty(out.shape, dtype=dtype, pin_memory=True)
+    lse_shape = (B, Hq, S) if kind == "fwd" else (B, Hq)
+    lse_host = torch.empty(lse_shape, dtype=torch.float32, pin_memory=True)
+    seq_host = host.get("seqlens")
     e2e_steps = max(2, min(args.steps, 5))
 
     def e2e_step():
-        nonlocal lse_host
-        for k_ in host:
-            d[k_].copy_(host[k_], non_blocking=True)
-        o, lse = step()
-        out_host.copy_(o, non_blocking=True)
-        if lse_host is None:
-            lse_host = torch.empty(lse.shape, dtype=lse.dtype, pin_memory=True)
-        lse_host.copy_(lse, non_blocking=True)
+        if kind == "fwd":
+            sfa.fwd_host(host["q"], host["k"], host["v"], causal=causal, out=out_host, lse=lse_host, device=dev)
+        else:
+            sfa.decode_host(host["q"], host["k"], host["v"], seq_host, out=out_host, lse=lse_host, device=dev)
     e2e_step()
     barrier()
+    launches_e2e0 = sfa.launch_count()
     e0.record()
     for _ in range(e2e_steps):
         e2e_step()
     e1.record()
     barrier()
+    launches_e2e = (sfa.launch_count() - launches_e2e0) // e2e_steps
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -276,7 +278,8 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (no flush)" if name != "c2" else "inputs 101 MB, L2-resident between steps",
                        "parallelism": f"batch x heads sharded, {world} independent rank(s), no collective"},
             "e2e": {"value": world * units["amount"] / (e2e_ms / 1e3), "unit": units["unit"],
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
+                    "api": "fwd_host" if kind == "fwd" else "decode_host", "launches_per_step": int(launches_e2e)},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": units["bound"], "achieved": per_gpu, "peak": peak,

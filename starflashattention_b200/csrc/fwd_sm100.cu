@@ -82,6 +82,23 @@ __device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
     return r;
 }
+// Order-pinned variants (asm volatile keeps their relative program order): the exp2 loop below is
+// software-pipelined by hand so that the MUFU, the softmax's critical unit, is fed at an even rate.
+__device__ __forceinline__ uint64_t ffma2_v(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ uint64_t fadd2_v(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm volatile("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ float ex2_v(float x) {
+    float y;
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
     uint64_t r;
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
@@ -127,14 +144,25 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
     }
 }
 
-// Register split of the three warpgroups when NQ == 2.  setmaxnreg.inc blocks until the CTA's own pool
-// (registers per thread at launch x 384 threads; 168 under __launch_bounds__(384, 1)) can cover the request, so
-// the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
-constexpr int kRegsLaunch = 168;
-constexpr int kRegsSoftmax = 216;
-constexpr int kRegsOther = 72;
-static_assert(2 * 128 * kRegsSoftmax + 128 * kRegsOther <= 384 * kRegsLaunch, "register split exceeds the CTA pool");
-static_assert(kRegsSoftmax % 8 == 0 && kRegsOther % 8 == 0, "setmaxnreg takes multiples of 8");
+// Register split between the softmax warpgroups and the warpgroup holding the TMA / MMA warps (NQ == 2 only).
+// setmaxnreg.inc blocks until the CTA's own pool (registers per thread at launch x threads) can cover the
+// request, so the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
+template <int NQ, int SPLIT>
+struct FwdRegs {
+    static constexpr int kThreads = NQ * SPLIT * 128 + (NQ == 2 ? 128 : 64);
+    static constexpr bool kSet = NQ == 2;
+    // registers ptxas may use at launch: floor(65536 / threads) rounded down to a multiple of 8
+    static constexpr int kLaunch = (65536 / kThreads) / 8 * 8;
+    static constexpr int kSoftmax = SPLIT == 2 ? 104 : 216;
+    static constexpr int kOther = SPLIT == 2 ? 64 : 72;
+    static_assert(!kSet || NQ * SPLIT * 128 * kSoftmax + 128 * kOther <= kThreads * kLaunch,
+                  "register split exceeds the CTA pool");
+    static_assert(kSoftmax % 8 == 0 && kOther % 8 == 0, "setmaxnreg takes multiples of 8");
+};
+
+__device__ __forceinline__ void named_barrier_sync(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
 template <int D, int NQ, int NSTAGE>
 struct FwdSmem {
@@ -143,24 +171,28 @@ struct FwdSmem {
     static constexpr int kQOff = 0;
     static constexpr int kRingOff = NQ * kTileBytes;
     static constexpr int kBarOff = kRingOff + NSTAGE * kTileBytes;
-    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ], o_final[NQ]
-    static constexpr int kNumBars = 4 * NQ + 2 * NSTAGE;
+    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], o_final[NQ]
+    static constexpr int kNumBars = 5 * NQ + 2 * NSTAGE;
     static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
-    static constexpr int kBytes = kTmemPtrOff + 16;
+    static constexpr int kXchOff = kTmemPtrOff + 16;                 // [2][NQ][2][128] floats (SPLIT == 2 row exchange)
+    static constexpr int kBytes = kXchOff + 2 * NQ * 2 * kBlockM * 4;
     static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
 };
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
 // DBG: 0 = product; 1..3 = timing probes that give wrong results (see tools/fwd_probe.py).
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
-__global__ void __launch_bounds__(NQ == 2 ? 384 : 192, 1)
+// SPLIT: warpgroups per query tile (2 = two threads per row, each 64 score columns and half of the output).
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG, int SPLIT>
+__global__ void __launch_bounds__(FwdRegs<NQ, SPLIT>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const FwdParams p) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    constexpr int kSoftmaxWarps = 4 * NQ;
+    using R = FwdRegs<NQ, SPLIT>;
+    constexpr bool kSetRegs = R::kSet;
+    constexpr int kSoftmaxWarps = 4 * NQ * SPLIT;
     constexpr int kTmemCols = (NQ * (kBlockN + D)) <= 256 ? 256 : 512;
     constexpr int kSub = D / 64;
-    constexpr bool kFreeRun = DBG == 4 || DBG == 6 || DBG == 7;   // probes: MMA warp never waits for P
+    constexpr bool kFreeRun = DBG == 4 || DBG == 6 || DBG == 7 || DBG == 8;   // probes: MMA warp never waits for P
     constexpr bool kProbe = DBG >= 4;
 
     extern __shared__ uint8_t smem_raw[];
@@ -171,8 +203,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     auto bar_kv_full = [&](int s) { return bar_base + 8u * (NQ + s); };
     auto bar_kv_empty = [&](int s) { return bar_base + 8u * (NQ + NSTAGE + s); };
     auto bar_s_full = [&](int q) { return bar_base + 8u * (NQ + 2 * NSTAGE + q); };
-    auto bar_p_ready = [&](int q) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + q); };
-    auto bar_o_final = [&](int q) { return bar_base + 8u * (3 * NQ + 2 * NSTAGE + q); };
+    // P is handed to the MMA warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
+    auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + 2 * q + half); };
+    auto bar_o_final = [&](int q) { return bar_base + 8u * (4 * NQ + 2 * NSTAGE + q); };
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -208,7 +241,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         for (int q = 0; q < NQ; ++q) {
             mbar_init(bar_q_full(q), 1);
             mbar_init(bar_s_full(q), 1);
-            mbar_init(bar_p_ready(q), 4);        // one elected arrival per softmax warp
+            mbar_init(bar_p_ready(q, 0), 4);   // one elected arrival per softmax warp of the half's warpgroup
+            mbar_init(bar_p_ready(q, 1), 4);
             mbar_init(bar_o_final(q), 1);
         }
 #pragma unroll
@@ -217,6 +251,25 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             mbar_init(bar_kv_empty(s), 1);
         }
         fence_barrier_init();
+        // The first loads need nobody's consent (the ring starts empty): issue them before the CTA-wide sync so
+        // that their latency overlaps the TMEM allocation and the rest of the prologue.
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            if (n_tiles[q] == 0) continue;
+            mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
+#pragma unroll
+            for (int s = 0; s < kSub; ++s)
+                tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
+                            64 * s, h, m0 + q * kBlockM, b);
+        }
+        for (int i = 0; i < min(NSTAGE, 2 * n_max); ++i) {
+            mbar_arrive_expect_tx(bar_kv_full(i), L::kTileBytes);
+            const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+#pragma unroll
+            for (int s = 0; s < kSub; ++s)
+                tma_load_4d(smem_base + L::kRingOff + i * L::kTileBytes + s * L::kSubTileBytes, map, bar_kv_full(i),
+                            64 * s, hk, (i >> 1) * kBlockN, b);
+        }
     }
     if (warp == kSoftmaxWarps + 1) {
         tmem_alloc(smem_base + L::kTmemPtrOff, kTmemCols);
@@ -231,22 +284,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     // warps) so the register file can be re-split: the softmax warpgroups take what the others give up.
     if (warp == kSoftmaxWarps) {
         // =============================================================== TMA producer
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
-        // whole warp in the loop (uniform control flow), one elected lane issues
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
+        // whole warp in the loop (uniform control flow), one elected lane issues; Q and the first NSTAGE
+        // tiles were issued in the prologue
         {
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                if (n_tiles[q] == 0) continue;
-                if (elect_one()) {
-                    mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
-#pragma unroll
-                    for (int s = 0; s < kSub; ++s)
-                        tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
-                                    64 * s, h, m0 + q * kBlockM, b);
-                }
-                __syncwarp();
-            }
-            for (int i = 0; i < 2 * n_max; ++i) {
+            for (int i = NSTAGE; i < 2 * n_max; ++i) {
                 const int slot = i % NSTAGE, use = i / NSTAGE;
                 if (!__all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1))) break;
                 if (elect_one()) {
@@ -262,7 +304,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
     } else if (warp == kSoftmaxWarps + 1) {
         // =============================================================== tcgen05 issuer
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         // The whole warp runs the loop (uniform control flow keeps descriptors in uniform registers); one elected
         // lane issues.  Descriptors are built once per operand tile and advanced by compile-time constants.
         {
@@ -284,18 +326,25 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 const uint32_t s_tmem = tmem_base + q * kBlockN;
 #pragma unroll
                 for (int kc = 0; kc < D / 16; ++kc) {
-                    constexpr int dummy = 0; (void)dummy;
                     const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
-                    mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_qk, kc > 0);
+                    if constexpr (DBG == 8) {   // probe: the same tile as two N = 64 halves (keys 0-63, 64-127)
+                        constexpr uint32_t idesc_half = mma_idesc(BF16, 0, 0, kBlockM, kBlockN / 2);
+                        mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_half, kc > 0);
+                        mma_ss(s_tmem + 64, q_desc[q] + off16, k_desc + off16 + (64 * 128 >> 4), idesc_half, kc > 0);
+                    } else {
+                        mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_qk, kc > 0);
+                    }
                 }
             };
-            auto issue_pv = [&](int q, int slot, bool accumulate) {
+            auto issue_pv = [&](int q, int slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
                 const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
                 const uint32_t p_tmem = tmem_base + q * kBlockN;
                 const uint32_t o_tmem = tmem_base + NQ * kBlockN + q * D;
 #pragma unroll
-                for (int kc = 0; kc < kBlockN / 16; ++kc)
+                for (int kk = 0; kk < kBlockN / 32; ++kk) {
+                    const int kc = half * (kBlockN / 32) + kk;
                     mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, accumulate || kc > 0);
+                }
             };
             auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
                 return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
@@ -330,11 +379,17 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 for (int q = 0; q < NQ; ++q) {
                     if (ok && j < n_tiles[q]) {
                         if constexpr (kProbe) c0 = clock64();
-                        if constexpr (!kFreeRun) ok = wait_all(bar_p_ready(q), j & 1, 5);
+                        if constexpr (!kFreeRun) ok = wait_all(bar_p_ready(q, 0), j & 1, 5);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            if constexpr (DBG != 6 && DBG != 8) issue_pv(q, vslot, 0, j > 0);
+                        }
+                        __syncwarp();
+                        if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 1), j & 1, 5);
                         if constexpr (kProbe) mt_p[q] += clock64() - c0;
                         tc_fence_after();
                         if (elect_one()) {
-                            if constexpr (DBG != 6) issue_pv(q, vslot, j > 0);
+                            if constexpr (DBG != 6 && DBG != 8) issue_pv(q, vslot, 1, true);
                             if (j == n_tiles[q] - 1) tc_commit(bar_o_final(q));
                             if (q == NQ - 1) tc_commit(bar_kv_empty(vslot));
                         }
@@ -370,13 +425,20 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
     } else if (warp < kSoftmaxWarps) {
         // =============================================================== softmax warpgroups
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSoftmax));
-        const int q = warp >> 2;
+        // Warpgroup wg serves query tile wg / SPLIT and, of every row, the score columns
+        // [part * kCols, (part + 1) * kCols) and the output columns [part * kOCols, ...), part = wg % SPLIT.
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(R::kSoftmax));
+        constexpr int kCols = kBlockN / SPLIT;
+        constexpr int kOCols = D / SPLIT;
+        const int wg = warp >> 2;
+        const int q = wg / SPLIT, part = wg % SPLIT;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const int row = m0 + q * kBlockM + row_in_tile;
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        const uint32_t s_tmem = lane_base + q * kBlockN;
-        const uint32_t o_tmem = lane_base + NQ * kBlockN + q * D;
+        const uint32_t s_tmem = lane_base + q * kBlockN + part * kCols;          // my score columns
+        const uint32_t p_tmem = lane_base + q * kBlockN + part * (kCols / 2);    // my packed P columns
+        const uint32_t o_tmem = lane_base + NQ * kBlockN + q * D + part * kOCols;
+        float* xch = reinterpret_cast<float*>(smem_gen + L::kXchOff);            // [2][NQ][2][128] row exchange
         const int n_q = n_tiles[q];
         const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
         const float sl2 = p.scale_log2;
@@ -396,49 +458,48 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_p_ready(q));
+                if (lane == 0) {
+                    if (SPLIT == 1 || part == 0) mbar_arrive(bar_p_ready(q, 0));
+                    if (SPLIT == 1 || part == 1) mbar_arrive(bar_p_ready(q, 1));
+                }
                 continue;
             }
-            uint32_t su[kBlockN];
-            tmem_ld32(s_tmem, &su[0]);
-            tmem_ld32(s_tmem + 32, &su[32]);
-            tmem_wait_ld();
-            tmem_ld32(s_tmem + 64, &su[64]);
-            tmem_ld32(s_tmem + 96, &su[96]);
-            if constexpr (DBG == 3) {      // TMEM traffic probe: load S, store raw halves back as P
-                tmem_wait_ld();
-                uint32_t pk[kBlockN / 2];
+            uint32_t su[kCols];
 #pragma unroll
-                for (int c = 0; c < kBlockN / 2; ++c) pk[c] = __byte_perm(su[2 * c], su[2 * c + 1], 0x7632);
-                tmem_st32(s_tmem, &pk[0]);
-                tmem_st32(s_tmem + 32, &pk[32]);
-                tmem_wait_st();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_p_ready(q));
-                continue;
-            }
+            for (int c = 0; c < kCols / 2; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+            tmem_wait_ld();
+#pragma unroll
+            for (int c = kCols / 2; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
 
             const int key0 = j * kBlockN;
             const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
                                    (key0 + kBlockN > p.seqlen_k);
-            const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
+            // my columns <= lim stay (masked tiles only)
+            const int lim = min(key_limit, p.seqlen_k - 1) - key0 - part * kCols;
             // ---- row maximum: four independent chains, first half while the second half is in flight
             float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
             auto scan_half = [&](int base) {
                 if (need_mask) {
 #pragma unroll
-                    for (int c = base; c < base + kBlockN / 2; ++c)
+                    for (int c = base; c < base + kCols / 2; ++c)
                         if (c > lim) su[c] = 0xff800000u;   // -inf
                 }
 #pragma unroll
-                for (int c = base; c < base + kBlockN / 2; c += 2)
+                for (int c = base; c < base + kCols / 2; c += 2)
                     mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
             };
             scan_half(0);
             tmem_wait_ld();
-            scan_half(kBlockN / 2);
-            const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+            scan_half(kCols / 2);
+            float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+            if constexpr (SPLIT == 2) {
+                // The two threads of a row swap their partial maxima (double-buffered by tile parity).  The
+                // barrier also orders my partner's S loads before my P store into its columns.
+                float* slot = xch + (((j & 1) * NQ + q) * 2) * kBlockM;
+                slot[part * kBlockM + row_in_tile] = mx_all;
+                named_barrier_sync(1 + q, 256);
+                mx_all = fmaxf(mx_all, slot[(part ^ 1) * kBlockM + row_in_tile]);
+            }
 
             const float m_new = fmaxf(m_used, mx_all);
             if (j == 0) {
@@ -452,13 +513,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     l_acc[1] = fmul2(l_acc[1], alpha2);
                     if (grow) m_used = m_new;
 #pragma unroll
-                    for (int c = 0; c < D / 32; ++c) {
-                        uint32_t o[32];
-                        tmem_ld32(o_tmem + 32 * c, o);
+                    for (int c = 0; c < kOCols / 16; ++c) {   // 16-column chunks: the scores stay in registers
+                        uint32_t o[16];
+                        tmem_ld16(o_tmem + 16 * c, o);
                         tmem_wait_ld();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                        tmem_st32(o_tmem + 32 * c, o);
+                        for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st16(o_tmem + 16 * c, o);
                     }
                 }
             }
@@ -466,44 +527,55 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
             if constexpr (DBG == 5) pt2 = clock64();
             // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
-            // pairs on tiles without masked (-inf) entries; P leaves for TMEM in two halves of 64 keys.
+            // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
             auto exp_and_store = [&](auto poly_tag) {
                 constexpr int kPoly = decltype(poly_tag)::value;
+                constexpr int kPairs = kCols / 2;
+                constexpr int kAhead = 3;            // pairs between the scale FFMA2 and its MUFUs
+                uint64_t xq[kAhead];                 // scaled scores waiting for their exp2
+                auto scale = [&](int i) {
+                    return ffma2_v(pack_f2(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), sl2_2, neg_m2);
+                };
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t pk[kBlockN / 4];
+                for (int i = 0; i < kAhead; ++i) xq[i] = scale(i);
+                uint32_t pk[32];
 #pragma unroll
-                    for (int i = 0; i < kBlockN / 4; ++i) {
-                        const int c = half * (kBlockN / 2) + 2 * i;
-                        const uint64_t x2 =
-                            ffma2(pack_f2(__uint_as_float(su[c]), __uint_as_float(su[c + 1])), sl2_2, neg_m2);
-                        float x0, x1, p0, p1;
-                        unpack_f2(x2, x0, x1);
-                        if constexpr (DBG == 1) {
-                            p0 = x0; p1 = x1;
-                        } else if ((i & 7) >= 8 - kPoly) {
-                            unpack_f2(exp2_poly2(x0, x1), p0, p1);
-                        } else {
-                            p0 = ex2(x0); p1 = ex2(x1);
-                        }
-                        l_acc[i & 1] = fadd2(l_acc[i & 1], pack_f2(p0, p1));
-                        pk[i] = pack_pair<BF16>(p0, p1);
+                for (int i = 0; i < kPairs; ++i) {
+                    float x0, x1, p0, p1;
+                    unpack_f2(xq[i % kAhead], x0, x1);
+                    if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
+                    if constexpr (DBG == 1) {
+                        p0 = x0; p1 = x1;
+                    } else if ((i & 7) >= 8 - kPoly) {
+                        unpack_f2(exp2_poly2(x0, x1), p0, p1);
+                    } else {
+                        p0 = ex2_v(x0); p1 = ex2_v(x1);
                     }
-                    tmem_st32(s_tmem + 32 * half, pk);
+                    l_acc[i & 1] = fadd2_v(l_acc[i & 1], pack_f2(p0, p1));
+                    pk[i & 31] = pack_pair<BF16>(p0, p1);
+                    if ((i & 31) == 31) tmem_st32(p_tmem + (i >> 5) * 32, pk);
+                    // the hand-off of a 64-key block trails its store by a few pairs, so that the MUFU keeps
+                    // running while the store drains (the last block has nothing left to overlap with)
+                    constexpr int kTrail = 6;
+                    if (((i & 31) == ((31 + kTrail) & 31) && i > 31) || i == kPairs - 1) {
+                        tmem_wait_st();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, part * (kCols / 64) + (kPairs / 32 - 1)));
+                            else mbar_arrive(bar_p_ready(q, part * (kCols / 64) + (i >> 5) - 1));
+                        }
+                    }
                 }
             };
             if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
             else exp_and_store(std::integral_constant<int, 0>{});
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_p_ready(q));
             if constexpr (DBG == 5) {
                 const long long pt3 = clock64();
                 pt_wait += pt1 - pt0; pt_max += pt2 - pt1; pt_exp += pt3 - pt2;
             }
         }
-        if (probe) {
+        if (probe && part == 0) {
             g_fwd_probe[8 * q + 0] = pt_wait; g_fwd_probe[8 * q + 1] = pt_max; g_fwd_probe[8 * q + 2] = pt_exp;
             g_fwd_probe[8 * q + 3] = n_q;
         }
@@ -512,15 +584,23 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         float l0, l1, l2, l3;
         unpack_f2(l_acc[0], l0, l1);
         unpack_f2(l_acc[1], l2, l3);
-        const float l_sum = (l0 + l1) + (l2 + l3);
+        float l_sum = (l0 + l1) + (l2 + l3);
+        if constexpr (SPLIT == 2) {
+            // both parity buffers are quiescent after one more barrier; use buffer 0 of this query tile
+            named_barrier_sync(1 + q, 256);
+            float* slot = xch + (q * 2) * kBlockM;
+            slot[part * kBlockM + row_in_tile] = l_sum;
+            named_barrier_sync(1 + q, 256);
+            l_sum += slot[(part ^ 1) * kBlockM + row_in_tile];
+        }
         const bool row_ok = row < p.seqlen_q;
         const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
         uint8_t* o_row = reinterpret_cast<uint8_t*>(p.o) +
-                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs);
+                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs + part * kOCols);
         if (n_q > 0 && ok) ok = wait_barrier(bar_o_final(q), 0, p.error_flag, 8);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
+        for (int c = 0; c < kOCols / 32; ++c) {
             uint32_t o[32];
             if (n_q > 0) {
                 tmem_ld32(o_tmem + 32 * c, o);
@@ -540,14 +620,14 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
             }
         }
-        if (row_ok && p.lse) {
+        if (row_ok && p.lse && part == 0) {
             const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
             p.lse[((int64_t)b * p.heads_q + h) * p.seqlen_q + row] = lse;
         }
     }
 
     else {
-        if constexpr (NQ == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));   // idle warps of the third warpgroup
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warps of the third warpgroup
     }
 
     // ---- teardown: every tcgen05 operation of this CTA has completed once the softmax warps are here
@@ -596,11 +676,11 @@ int make_map(CUtensorMap* map, const void* base, int dtype, int head_dim, int he
     return SFA_OK;
 }
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG, int SPLIT = 1>
 int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p,
                     int batch, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG, SPLIT>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -609,7 +689,7 @@ int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensor
     SFA_CUDA_CHECK(attr_err);
     const int m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     dim3 grid(m_blocks, p.heads_q, batch);
-    kern<<<grid, NQ == 2 ? 384 : 192, L::kAlloc, stream>>>(qm, km, vm, p);
+    kern<<<grid, FwdRegs<NQ, SPLIT>::kThreads, L::kAlloc, stream>>>(qm, km, vm, p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return SFA_OK;
@@ -617,37 +697,49 @@ int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensor
 
 // Host launcher: the tile configuration per (head_dim, rows, dtype).  kPolyDefault of every 8 column pairs
 // take the polynomial exp2 (the MUFU is co-critical with the tensor pipe at head_dim 128 and dominant at 64).
-constexpr int kPolyDefault128 = 2;
-constexpr int kPolyDefault64 = 3;
+constexpr int kSplitDefault = 1;
 
 template <bool BF16>
 int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p, int batch,
                  int head_dim, int nq, cudaStream_t stream) {
-    // Tuning / probe overrides (tools/fwd_probe.py): SFA_FWD_POLY in {0,2,3,4}, SFA_FWD_DBG in {1,2,3}; bf16 d=128 NQ=2 only.
+    // Tuning / probe overrides (tools/fwd_time.py): SFA_FWD_SPLIT in {1,2}, SFA_FWD_POLY in {0,2,3,4},
+    // SFA_FWD_DBG probes (bf16, head_dim 128, two query tiles only).
     static const int poly = [] { const char* e = getenv("SFA_FWD_POLY"); return e ? atoi(e) : -1; }();
     static const int dbg = [] { const char* e = getenv("SFA_FWD_DBG"); return e ? atoi(e) : 0; }();
+    static const int split = [] { const char* e = getenv("SFA_FWD_SPLIT"); return e ? atoi(e) : kSplitDefault; }();
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DBG_, SPLIT_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DBG_, SPLIT_>(qm, km, vm, p, batch, stream)
     if (head_dim == 128) {
-        if (nq == 1) return launch_instance<128, 1, 4, BF16, kPolyDefault128, 0>(qm, km, vm, p, batch, stream);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 0, 1);
         if constexpr (BF16) {
-            if (dbg == 1) return launch_instance<128, 2, 4, true, 0, 1>(qm, km, vm, p, batch, stream);
-            if (dbg == 2) return launch_instance<128, 2, 4, true, 0, 2>(qm, km, vm, p, batch, stream);
-            if (dbg == 3) return launch_instance<128, 2, 4, true, 0, 3>(qm, km, vm, p, batch, stream);
-            if (dbg == 4) return launch_instance<128, 2, 4, true, 0, 4>(qm, km, vm, p, batch, stream);
-            if (dbg == 5) return launch_instance<128, 2, 4, true, 0, 5>(qm, km, vm, p, batch, stream);
-            if (dbg == 6) return launch_instance<128, 2, 4, true, 0, 6>(qm, km, vm, p, batch, stream);
-            if (dbg == 7) return launch_instance<128, 2, 4, true, 0, 7>(qm, km, vm, p, batch, stream);
-            if (poly == 0) return launch_instance<128, 2, 4, true, 0, 0>(qm, km, vm, p, batch, stream);
-            if (poly == 3) return launch_instance<128, 2, 4, true, 3, 0>(qm, km, vm, p, batch, stream);
-            if (poly == 4) return launch_instance<128, 2, 4, true, 4, 0>(qm, km, vm, p, batch, stream);
+            if (split == 2) {
+                if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2, 2);
+                if (dbg == 5 && poly == 2) SFA_LAUNCH(128, 2, 4, 2, 5, 2);
+                if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5, 2);
+                if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0, 2);
+                if (poly == 3) SFA_LAUNCH(128, 2, 4, 3, 0, 2);
+                if (poly == 4) SFA_LAUNCH(128, 2, 4, 4, 0, 2);
+            } else {
+                if (dbg == 1) SFA_LAUNCH(128, 2, 4, 0, 1, 1);
+                if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2, 1);
+                if (dbg == 4) SFA_LAUNCH(128, 2, 4, 0, 4, 1);
+                if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5, 1);
+                if (dbg == 6) SFA_LAUNCH(128, 2, 4, 0, 6, 1);
+                if (dbg == 7) SFA_LAUNCH(128, 2, 4, 0, 7, 1);
+                if (dbg == 8) SFA_LAUNCH(128, 2, 4, 0, 8, 1);
+                if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0, 1);
+            }
         }
-        return launch_instance<128, 2, 4, BF16, kPolyDefault128, 0>(qm, km, vm, p, batch, stream);
+        if (split == 2) SFA_LAUNCH(128, 2, 4, 0, 0, 2);
+        SFA_LAUNCH(128, 2, 4, 0, 0, 1);
     }
-    if (nq == 1) return launch_instance<64, 1, 6, BF16, kPolyDefault64, 0>(qm, km, vm, p, batch, stream);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, 1);
     if constexpr (!BF16) {
-        if (poly == 0) return launch_instance<64, 2, 6, false, 0, 0>(qm, km, vm, p, batch, stream);
-        if (poly == 4) return launch_instance<64, 2, 6, false, 4, 0>(qm, km, vm, p, batch, stream);
+        if (split == 2 && poly == 3) SFA_LAUNCH(64, 2, 6, 3, 0, 2);
     }
-    return launch_instance<64, 2, 6, BF16, kPolyDefault64, 0>(qm, km, vm, p, batch, stream);
+    if (split == 2) SFA_LAUNCH(64, 2, 6, 0, 0, 2);
+    SFA_LAUNCH(64, 2, 6, 0, 0, 1);
+#undef SFA_LAUNCH
 }
 
 }  // namespace

@@ -278,3 +278,21 @@ def test_torch_extension_fwd_and_decode(torch_ext):
     o, lse = torch_ext.decode(qd.cuda(), kc.cuda(), vc.cuda(), sl.cuda())
     assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 2e-3
     assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+
+
+def test_decode_host_pipeline_matches_device_path():
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    B, Hq, Hkv, D, M = 5, 8, 2, 128, 3000
+    q = _rand((B, Hq, D), dtype, 41).pin_memory()
+    kc = _rand((B, M, Hkv, D), dtype, 42).pin_memory()
+    vc = _rand((B, M, Hkv, D), dtype, 43).pin_memory()
+    sl = torch.tensor([3000, 1, 777, 2048, 129], dtype=torch.int32).pin_memory()
+    o_h, lse_h = sfa.decode_host(q, kc, vc, sl, chunks=3)
+    o_d, lse_d = sfa.decode(q.cuda(), kc.cuda(), vc.cuda(), sl.cuda())
+    torch.cuda.synchronize()
+    o_ref, lse_ref = naive.decode_attention(q, kc, vc, sl)
+    _assert_close(o_h, o_ref, dtype, "decode_host O")
+    assert float((lse_h - lse_ref).abs().max()) <= 1e-3
+    # the split count may differ between a 2-sequence chunk and the 5-sequence batch: compare within rounding
+    assert float((o_h.float() - o_d.float().cpu()).abs().max()) <= 2e-2

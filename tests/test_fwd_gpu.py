@@ -167,3 +167,25 @@ def test_fwd_full_c2_shape_spot_check():
     torch.cuda.synchronize()
     assert torch.isfinite(o).all() and torch.isfinite(lse).all()
     _spot_check(q, k, v, o, lse, False, [0, 1000, 4095], [(0, 0), (3, 15)], dtype)
+
+
+@pytest.mark.parametrize("B,H,Hkv,chunks", [(4, 4, 2, None), (1, 8, 4, 3), (3, 2, 2, 2)])
+def test_fwd_host_pipeline_matches_device_path(B, H, Hkv, chunks):
+    """Pinned host tensors in, pinned host tensors out: the chunked three-stream pipeline must give exactly
+    what one device-resident call gives (the units are independent), and match the oracle."""
+    import starflashattention_b200 as sfa
+    dtype = torch.float16
+    q = _rand((B, 200, H, 128), dtype, 31).pin_memory()
+    k = _rand((B, 333, Hkv, 128), dtype, 32).pin_memory()
+    v = _rand((B, 333, Hkv, 128), dtype, 33).pin_memory()
+    o_h, lse_h = sfa.fwd_host(q, k, v, causal=True, chunks=chunks)
+    o_h2, lse_h2 = sfa.fwd_host(q, k, v, causal=True, chunks=chunks)      # second call reuses the staging buffers
+    o_d, lse_d = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=True)
+    torch.cuda.synchronize()
+    assert o_h.is_pinned() and lse_h.is_pinned()
+    assert torch.equal(o_h, o_d.cpu()) and torch.equal(lse_h, lse_d.cpu())
+    assert torch.equal(o_h2, o_h) and torch.equal(lse_h2, lse_h)
+    o_ref, lse_ref = naive.attention_fwd(q, k, v, causal=True)
+    _check(o_h, lse_h, o_ref, lse_ref, dtype, "fwd_host")
+    with pytest.raises(ValueError, match="pinned"):
+        sfa.fwd_host(q.clone(), k, v)

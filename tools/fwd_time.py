@@ -61,7 +61,7 @@ def main():
                f"{statistics.median(half):.0f} MHz min {min(sm)} max {max(sm)}, power max {max(pw):.0f} W")
     except Exception as e:  # noqa: BLE001
         clk = f" | clock sampling failed: {e!r}"
-    if os.environ.get("SFA_FWD_DBG") in ("4", "5", "6", "7"):
+    if os.environ.get("SFA_FWD_DBG") in ("4", "5", "6", "7", "8"):
         import ctypes
         from starflashattention_b200 import _capi
         buf = (ctypes.c_uint64 * 32)()
