@@ -13,9 +13,13 @@
 //   warp 4*NQ+1         tcgen05 issuer (one thread): S_q = Q_q K_j^T (SS, both operands K-major) and
 //                       O_q += P_q V_j (TS: A = P in TMEM, B = V in smem, MN-major); it also owns
 //                       the TMEM allocation
-// The two query tiles are interleaved in the issue order QK0_0 QK1_0 | PV0_0 QK0_1 | PV1_0 QK1_1 |
-// ... so that while one softmax warpgroup works on its S tile the tensor pipe runs the other
-// tile's MMAs (TMEM: S0 S1 O0 O1 = 4 x 128 columns at head_dim 128).
+// TMEM: P0 P1 | S | O0 O1 = 2 x 64 + 128 + 2 x 128 columns at head_dim 128.  P does not alias S: a
+// softmax warpgroup frees the score buffer as soon as its tcgen05.ld has landed in registers, so
+// the tensor pipe computes S(q, j+1) while the warpgroup is still exponentiating tile j.  The
+// softmax warpgroups therefore run back to back (throughput bound) instead of sitting in the
+// latency chain softmax -> P.V -> Q.K(next) of an aliased S/P layout.  Issue order of the MMA warp:
+// step (q, j), j-major: Q.K(q, j) then P.V(q, j-1).  The single score buffer alternates between
+// the two query tiles (head_dim 64 and the one-tile variant have room for two buffers).
 // O is rescaled lazily: the reference maximum of a row only moves when the true maximum has grown
 // by more than 2^8, so the TMEM read-modify-write of O is rare after the first tiles.
 #include "internal.h"
@@ -49,7 +53,7 @@ struct FwdParams {
 };
 
 __device__ int g_fwd_error;
-__device__ unsigned long long g_fwd_probe[32];   // DBG == 5: cycle counters of CTA (0,0,0), see tools/fwd_probe.py   // set when an mbarrier wait times out (pipeline bug guard)
+__device__ unsigned long long g_fwd_probe[32 + 2048];   // DBG == 5: cycle counters of CTA (0,0,0), see tools/fwd_probe.py   // set when an mbarrier wait times out (pipeline bug guard)
 
 // Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.
 __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
@@ -66,6 +70,12 @@ __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int*
         }
     }
     return true;
+}
+
+// DBG == 6: event trace of CTA (0,0,0): slot 32 + (j * 2 + q) * 16 + e holds clock64() of event e of tile (q, j).
+// Events 0-6 are written by the MMA warp, 8-12 by the first softmax warp of the tile's warpgroup.
+__device__ __forceinline__ void trace_event(bool on, int q, int j, int e) {
+    if (on && j < 64) g_fwd_probe[32 + (j * 2 + q) * 16 + e] = clock64();
 }
 
 // ---- packed fp32x2 arithmetic (FFMA2 / FADD2 / FMUL2 on sm_100): halves the issue slots of the softmax
@@ -147,22 +157,33 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
 // Register split between the softmax warpgroups and the warpgroup holding the TMA / MMA warps (NQ == 2 only).
 // setmaxnreg.inc blocks until the CTA's own pool (registers per thread at launch x threads) can cover the
 // request, so the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
-template <int NQ, int SPLIT>
+template <int NQ>
 struct FwdRegs {
-    static constexpr int kThreads = NQ * SPLIT * 128 + (NQ == 2 ? 128 : 64);
+    static constexpr int kThreads = NQ * 128 + (NQ == 2 ? 128 : 64);
     static constexpr bool kSet = NQ == 2;
     // registers ptxas may use at launch: floor(65536 / threads) rounded down to a multiple of 8
     static constexpr int kLaunch = (65536 / kThreads) / 8 * 8;
-    static constexpr int kSoftmax = SPLIT == 2 ? 104 : 216;
-    static constexpr int kOther = SPLIT == 2 ? 64 : 72;
-    static_assert(!kSet || NQ * SPLIT * 128 * kSoftmax + 128 * kOther <= kThreads * kLaunch,
+    static constexpr int kSoftmax = 216;
+    static constexpr int kOther = 72;
+    static_assert(!kSet || NQ * 128 * kSoftmax + 128 * kOther <= kThreads * kLaunch,
                   "register split exceeds the CTA pool");
     static_assert(kSoftmax % 8 == 0 && kOther % 8 == 0, "setmaxnreg takes multiples of 8");
 };
 
-__device__ __forceinline__ void named_barrier_sync(int id, int threads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
+constexpr int next_pow2_cols(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : n <= 256 ? 256 : 512; }
+
+// TMEM columns: P tiles (64 columns each: 128 keys as packed 16-bit pairs), score buffers, O accumulators.
+template <int D, int NQ>
+struct FwdTmem {
+    static constexpr int kPOff = 0;
+    static constexpr int kSOff = NQ * (kBlockN / 2);
+    // two score buffers wherever 512 columns allow it (everything but two query tiles at head_dim 128)
+    static constexpr int kSBufs = (kSOff + 2 * kBlockN + NQ * D <= 512) ? 2 : 1;
+    static constexpr int kOOff = kSOff + kSBufs * kBlockN;
+    static constexpr int kUsed = kOOff + NQ * D;
+    static constexpr int kCols = next_pow2_cols(kUsed);
+    static_assert(kUsed <= 512, "TMEM budget exceeded");
+};
 
 template <int D, int NQ, int NSTAGE>
 struct FwdSmem {
@@ -171,29 +192,30 @@ struct FwdSmem {
     static constexpr int kQOff = 0;
     static constexpr int kRingOff = NQ * kTileBytes;
     static constexpr int kBarOff = kRingOff + NSTAGE * kTileBytes;
-    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], o_final[NQ]
-    static constexpr int kNumBars = 5 * NQ + 2 * NSTAGE;
+    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], pv_done[NQ], s_free[2]
+    static constexpr int kNumBars = 5 * NQ + 2 * NSTAGE + 2;
     static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
-    static constexpr int kXchOff = kTmemPtrOff + 16;                 // [2][NQ][2][128] floats (SPLIT == 2 row exchange)
-    static constexpr int kBytes = kXchOff + 2 * NQ * 2 * kBlockM * 4;
+    static constexpr int kBytes = kTmemPtrOff + 16;
     static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
+    static_assert(kAlloc <= 232448, "shared memory budget exceeded");
 };
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-// DBG: 0 = product; 1..3 = timing probes that give wrong results (see tools/fwd_probe.py).
-// SPLIT: warpgroups per query tile (2 = two threads per row, each 64 score columns and half of the output).
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG, int SPLIT>
-__global__ void __launch_bounds__(FwdRegs<NQ, SPLIT>::kThreads, 1)
+// DBG: 0 = product; 1, 2, 4 = timing probes that give wrong results, 5 = cycle counters (tools/fwd_time.py).
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
+__global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const FwdParams p) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    using R = FwdRegs<NQ, SPLIT>;
+    using R = FwdRegs<NQ>;
+    using T = FwdTmem<D, NQ>;
     constexpr bool kSetRegs = R::kSet;
-    constexpr int kSoftmaxWarps = 4 * NQ * SPLIT;
-    constexpr int kTmemCols = (NQ * (kBlockN + D)) <= 256 ? 256 : 512;
+    constexpr int kSoftmaxWarps = 4 * NQ;
+    constexpr int kSBufs = T::kSBufs;
     constexpr int kSub = D / 64;
-    constexpr bool kFreeRun = DBG == 4 || DBG == 6 || DBG == 7 || DBG == 8;   // probes: MMA warp never waits for P
-    constexpr bool kProbe = DBG >= 4;
+    constexpr bool kFreeRun = DBG == 4;   // probe: the MMA warp never waits for the softmax warps
+    constexpr bool kProbe = DBG == 4 || DBG == 5;
+    constexpr bool kTrace = DBG == 6;
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -205,7 +227,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     auto bar_s_full = [&](int q) { return bar_base + 8u * (NQ + 2 * NSTAGE + q); };
     // P is handed to the MMA warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
     auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + 2 * q + half); };
-    auto bar_o_final = [&](int q) { return bar_base + 8u * (4 * NQ + 2 * NSTAGE + q); };
+    // every P.V of query tile q has completed: P(q) may be overwritten, O(q) may be rescaled / read
+    auto bar_pv_done = [&](int q) { return bar_base + 8u * (4 * NQ + 2 * NSTAGE + q); };
+    // warpgroup q has loaded its scores into registers: the next Q.K may overwrite that buffer
+    auto bar_s_free = [&](int q) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + q); };
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -232,6 +257,26 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         n_tiles[q] = n;
         n_max = max(n_max, n);
     }
+    // Q.K products are ordered j-major, q-minor; the k-th one writes score buffer k % kSBufs.
+    auto qk_ordinal = [&](int q, int j) {
+        int k = 0;
+#pragma unroll
+        for (int qq = 0; qq < NQ; ++qq) k += min(j, n_tiles[qq]) + ((qq < q && j < n_tiles[qq]) ? 1 : 0);
+        return k;
+    };
+    // inverse of qk_ordinal: (query tile << 16) | key tile
+    auto tile_of_ordinal = [&](int ord) {
+        const int n0 = n_tiles[0], n1 = n_tiles[NQ - 1], m = min(n0, n1);
+        if (ord < 2 * m) return ((ord & 1) << 16) | (ord >> 1);
+        return ((n0 > n1 ? 0 : 1) << 16) | (m + ord - 2 * m);
+    };
+    // Score buffer of tile (q, j): the single shared buffer (two query tiles at head_dim 128), else one buffer
+    // per query tile, else (one query tile) alternating buffers.
+    auto s_buffer = [&](int q, int j) { return kSBufs == 1 ? 0 : (NQ == 2 ? q : (j & 1)); };
+    // Barrier on which the warpgroup of tile (q, j) reports "scores loaded, buffer free".  Every barrier has
+    // exactly one waiter at a time and that waiter follows each of its phases in order, which is what a parity
+    // wait needs: per warpgroup when the buffer is shared or dedicated, per buffer when one tile alternates.
+    auto s_free_index = [&](int q, int j) { return NQ == 2 ? q : (j & 1); };
 
     if (warp == kSoftmaxWarps && lane == 0) {
         prefetch_tensormap(&q_map);
@@ -241,14 +286,16 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         for (int q = 0; q < NQ; ++q) {
             mbar_init(bar_q_full(q), 1);
             mbar_init(bar_s_full(q), 1);
-            mbar_init(bar_p_ready(q, 0), 4);   // one elected arrival per softmax warp of the half's warpgroup
+            mbar_init(bar_p_ready(q, 0), 4);   // one elected arrival per softmax warp of the tile's warpgroup
             mbar_init(bar_p_ready(q, 1), 4);
-            mbar_init(bar_o_final(q), 1);
+            mbar_init(bar_pv_done(q), 1);
         }
+        mbar_init(bar_s_free(0), 4);
+        mbar_init(bar_s_free(1), 4);
 #pragma unroll
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bar_kv_full(s), 1);
-            mbar_init(bar_kv_empty(s), 1);
+            mbar_init(bar_kv_empty(s), NQ);   // one arrival per query tile's MMA warp
         }
         fence_barrier_init();
         // The first loads need nobody's consent (the ring starts empty): issue them before the CTA-wide sync so
@@ -272,7 +319,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
     }
     if (warp == kSoftmaxWarps + 1) {
-        tmem_alloc(smem_base + L::kTmemPtrOff, kTmemCols);
+        tmem_alloc(smem_base + L::kTmemPtrOff, T::kCols);
         tmem_relinquish();
     }
     tc_fence_before();
@@ -287,159 +334,149 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         // whole warp in the loop (uniform control flow), one elected lane issues; Q and the first NSTAGE
         // tiles were issued in the prologue
-        {
-            for (int i = NSTAGE; i < 2 * n_max; ++i) {
-                const int slot = i % NSTAGE, use = i / NSTAGE;
-                if (!__all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1))) break;
-                if (elect_one()) {
-                    mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
-                    const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+        for (int i = NSTAGE; i < 2 * n_max; ++i) {
+            const int slot = i % NSTAGE, use = i / NSTAGE;
+            if (!__all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1))) break;
+            if (elect_one()) {
+                mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
+                const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
 #pragma unroll
-                    for (int s = 0; s < kSub; ++s)
-                        tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
-                                    bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
-                }
-                __syncwarp();
+                for (int s = 0; s < kSub; ++s)
+                    tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
+                                bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
             }
+            __syncwarp();
         }
-    } else if (warp == kSoftmaxWarps + 1) {
-        // =============================================================== tcgen05 issuer
+    } else if (warp > kSoftmaxWarps && warp <= kSoftmaxWarps + NQ) {
+        // =============================================================== tcgen05 issuers, one warp per query tile
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         // The whole warp runs the loop (uniform control flow keeps descriptors in uniform registers); one elected
         // lane issues.  Descriptors are built once per operand tile and advanced by compile-time constants.
-        {
-            constexpr uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
-            constexpr uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
-            // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
-            // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
-            constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
-            constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
-            const uint64_t ring_k_desc = smem_desc_at(desc_kmajor, smem_base + L::kRingOff);
-            const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
-            uint64_t q_desc[NQ];
+        constexpr uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
+        constexpr uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
+        // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
+        // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
+        constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
+        constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
+        const uint64_t ring_k_desc = smem_desc_at(desc_kmajor, smem_base + L::kRingOff);
+        const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
+        bool ok = true;
+        const int q = NQ == 1 ? 0 : warp - (kSoftmaxWarps + 1);   // the query tile this warp issues for
+        const int n_q = q == 0 ? n_tiles[0] : n_tiles[NQ - 1];
+        const uint64_t q_desc = smem_desc_at(desc_kmajor, smem_base + L::kQOff + q * L::kTileBytes);
+        // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
+        auto issue_qk = [&](int slot, int buf) {
+            const uint64_t k_desc = ring_k_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
+            const uint32_t s_tmem = tmem_base + T::kSOff + buf * kBlockN;
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) q_desc[q] = smem_desc_at(desc_kmajor, smem_base + L::kQOff + q * L::kTileBytes);
-            bool ok = true;
-            // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
-            auto issue_qk = [&](int q, int slot) {
-                const uint64_t k_desc = ring_k_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
-                const uint32_t s_tmem = tmem_base + q * kBlockN;
-#pragma unroll
-                for (int kc = 0; kc < D / 16; ++kc) {
-                    const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
-                    if constexpr (DBG == 8) {   // probe: the same tile as two N = 64 halves (keys 0-63, 64-127)
-                        constexpr uint32_t idesc_half = mma_idesc(BF16, 0, 0, kBlockM, kBlockN / 2);
-                        mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_half, kc > 0);
-                        mma_ss(s_tmem + 64, q_desc[q] + off16, k_desc + off16 + (64 * 128 >> 4), idesc_half, kc > 0);
-                    } else {
-                        mma_ss(s_tmem, q_desc[q] + off16, k_desc + off16, idesc_qk, kc > 0);
-                    }
-                }
-            };
-            auto issue_pv = [&](int q, int slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
-                const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
-                const uint32_t p_tmem = tmem_base + q * kBlockN;
-                const uint32_t o_tmem = tmem_base + NQ * kBlockN + q * D;
-#pragma unroll
-                for (int kk = 0; kk < kBlockN / 32; ++kk) {
-                    const int kc = half * (kBlockN / 32) + kk;
-                    mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, accumulate || kc > 0);
-                }
-            };
-            auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
-                return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
-            };
-            if (n_max > 0) {
-                ok = wait_all(bar_kv_full(0), 0, 2);
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) {
-                    if (!ok || n_tiles[q] == 0) continue;
-                    ok = wait_all(bar_q_full(q), 0, 3);
-                    tc_fence_after();
-                    if (elect_one()) {
-                        issue_qk(q, 0);
-                        tc_commit(bar_s_full(q));
-                    }
-                    __syncwarp();
-                }
-                if (elect_one()) tc_commit(bar_kv_empty(0));
-                __syncwarp();
+            for (int kc = 0; kc < D / 16; ++kc) {
+                const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
+                mma_ss(s_tmem, q_desc + off16, k_desc + off16, idesc_qk, kc > 0);
             }
-            long long mt_p[2] = {0, 0}, mt_kv = 0, mt_total = clock64();
-            for (int j = 0; j < n_max && ok; ++j) {
-                const int vi = 2 * j + 1, ki = 2 * j + 2;
-                const int vslot = vi % NSTAGE, kslot = ki % NSTAGE;
-                const bool have_next = j + 1 < n_max;
-                long long c0 = 0;
+        };
+        auto issue_pv = [&](int slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
+            const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
+            const uint32_t p_tmem = tmem_base + T::kPOff + q * (kBlockN / 2);
+            const uint32_t o_tmem = tmem_base + T::kOOff + q * D;
+#pragma unroll
+            for (int kk = 0; kk < kBlockN / 32; ++kk) {
+                const int kc = half * (kBlockN / 32) + kk;
+                mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, accumulate || kc > 0);
+            }
+        };
+        auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
+            return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
+        };
+        // A ring slot is handed back with one arrival per query tile; where the other tile does not use key tile
+        // j (causal tail, or a query tile past the end of Q) this warp arrives for it as well.
+        auto users = [&](int j) {
+            int u = 0;
+#pragma unroll
+            for (int qq = 0; qq < NQ; ++qq) u += j < n_tiles[qq] ? 1 : 0;
+            return u;
+        };
+        long long mt_p = 0, mt_kv = 0, mt_sfree = 0, mt_total = clock64(), c0 = 0;
+        const bool tre = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+        const bool tr = tre && lane == 0;
+        if (n_q > 0) ok = wait_all(bar_q_full(q), 0, 3);
+        for (int j = 0; j <= n_q && ok; ++j) {
+            // ---- S(q, j) = Q_q K_j^T
+            if (j < n_q) {
+                const int ki = 2 * j, kslot = ki % NSTAGE;
+                const int ord = qk_ordinal(q, j), buf = s_buffer(q, j);
+                trace_event(tr, q, j, 7);
+                if constexpr (kProbe) c0 = clock64();
+                ok = wait_all(bar_kv_full(kslot), (ki / NSTAGE) & 1, 2);
+                if constexpr (kProbe) { mt_kv += clock64() - c0; c0 = clock64(); }
+                trace_event(tr, q, j, 0);
+                if constexpr (!kFreeRun) {
+                    // the buffer's previous scores must have been loaded into registers by their warpgroup
+                    if constexpr (NQ == 2 && kSBufs == 1) {
+                        if (ord >= 1) {
+                            const int prev = tile_of_ordinal(ord - 1);
+                            ok = ok && wait_all(bar_s_free(prev >> 16), prev & 1, 9);
+                        }
+                    } else if constexpr (NQ == 2) {
+                        if (j >= 1) ok = ok && wait_all(bar_s_free(q), (j - 1) & 1, 9);
+                    } else {
+                        if (j >= 2) ok = ok && wait_all(bar_s_free(j & 1), ((j >> 1) - 1) & 1, 9);
+                    }
+                }
+                if constexpr (kProbe) mt_sfree += clock64() - c0;
+                tc_fence_after();
+                trace_event(tr, q, j, 1);
+                if (ok && elect_one()) {
+                    issue_qk(kslot, buf);
+                    trace_event(tre, q, j, 13);
+                    tc_commit(bar_s_full(q));
+                    for (int u = users(j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
+                }
+                __syncwarp();
+                trace_event(tr, q, j, 2);
+            }
+            // ---- O(q) += P(q, j-1) V_{j-1}, in two halves of 64 keys
+            if (ok && j > 0) {
+                const int vi = 2 * j - 1, vslot = vi % NSTAGE;
                 if constexpr (kProbe) c0 = clock64();
                 ok = wait_all(bar_kv_full(vslot), (vi / NSTAGE) & 1, 4);
-                if constexpr (kProbe) mt_kv += clock64() - c0;
-                bool k_waited = false;
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) {
-                    if (ok && j < n_tiles[q]) {
-                        if constexpr (kProbe) c0 = clock64();
-                        if constexpr (!kFreeRun) ok = wait_all(bar_p_ready(q, 0), j & 1, 5);
-                        tc_fence_after();
-                        if (elect_one()) {
-                            if constexpr (DBG != 6 && DBG != 8) issue_pv(q, vslot, 0, j > 0);
-                        }
-                        __syncwarp();
-                        if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 1), j & 1, 5);
-                        if constexpr (kProbe) mt_p[q] += clock64() - c0;
-                        tc_fence_after();
-                        if (elect_one()) {
-                            if constexpr (DBG != 6 && DBG != 8) issue_pv(q, vslot, 1, true);
-                            if (j == n_tiles[q] - 1) tc_commit(bar_o_final(q));
-                            if (q == NQ - 1) tc_commit(bar_kv_empty(vslot));
-                        }
-                        __syncwarp();
-                    } else if (q == NQ - 1) {
-                        if (elect_one()) tc_commit(bar_kv_empty(vslot));
-                        __syncwarp();
-                    }
-                    if (ok && j + 1 < n_tiles[q]) {
-                        if (!k_waited) {
-                            if constexpr (kProbe) c0 = clock64();
-                            ok = wait_all(bar_kv_full(kslot), (ki / NSTAGE) & 1, 6);
-                            if constexpr (kProbe) mt_kv += clock64() - c0;
-                            tc_fence_after();
-                            k_waited = true;
-                        }
-                        if (elect_one()) {
-                            if constexpr (DBG != 7) issue_qk(q, kslot);
-                            tc_commit(bar_s_full(q));
-                            if (q == NQ - 1 && have_next) tc_commit(bar_kv_empty(kslot));
-                        }
-                        __syncwarp();
-                    } else if (q == NQ - 1 && have_next) {
-                        if (elect_one()) tc_commit(bar_kv_empty(kslot));
-                        __syncwarp();
-                    }
+                if constexpr (kProbe) { mt_kv += clock64() - c0; c0 = clock64(); }
+                trace_event(tr, q, j - 1, 14);
+                if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 0), (j - 1) & 1, 5);
+                tc_fence_after();
+                trace_event(tr, q, j - 1, 3);
+                if (ok && elect_one()) issue_pv(vslot, 0, j > 1);
+                __syncwarp();
+                trace_event(tr, q, j - 1, 4);
+                if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 1), (j - 1) & 1, 5);
+                if constexpr (kProbe) mt_p += clock64() - c0;
+                tc_fence_after();
+                trace_event(tr, q, j - 1, 5);
+                if (ok && elect_one()) {
+                    issue_pv(vslot, 1, true);
+                    trace_event(tre, q, j - 1, 15);
+                    tc_commit(bar_pv_done(q));
+                    for (int u = users(j - 1); u <= NQ; ++u) tc_commit(bar_kv_empty(vslot));
                 }
+                __syncwarp();
+                trace_event(tr, q, j - 1, 6);
             }
-            if (kProbe && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
-                g_fwd_probe[16] = mt_p[0]; g_fwd_probe[17] = mt_p[NQ - 1]; g_fwd_probe[18] = mt_kv;
-                g_fwd_probe[19] = clock64() - mt_total; g_fwd_probe[20] = n_max;
-            }
+        }
+        if (kProbe && q == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+            g_fwd_probe[16] = mt_p; g_fwd_probe[17] = mt_sfree; g_fwd_probe[18] = mt_kv;
+            g_fwd_probe[19] = clock64() - mt_total; g_fwd_probe[20] = n_q;
         }
     } else if (warp < kSoftmaxWarps) {
         // =============================================================== softmax warpgroups
-        // Warpgroup wg serves query tile wg / SPLIT and, of every row, the score columns
-        // [part * kCols, (part + 1) * kCols) and the output columns [part * kOCols, ...), part = wg % SPLIT.
+        // Warpgroup q serves query tile q; thread i owns row i of the tile (TMEM lane i).
         if constexpr (kSetRegs) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(R::kSoftmax));
-        constexpr int kCols = kBlockN / SPLIT;
-        constexpr int kOCols = D / SPLIT;
-        const int wg = warp >> 2;
-        const int q = wg / SPLIT, part = wg % SPLIT;
+        constexpr int kCols = kBlockN;
+        const int q = warp >> 2;
         const int row_in_tile = (warp & 3) * 32 + lane;
         const int row = m0 + q * kBlockM + row_in_tile;
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-        const uint32_t s_tmem = lane_base + q * kBlockN + part * kCols;          // my score columns
-        const uint32_t p_tmem = lane_base + q * kBlockN + part * (kCols / 2);    // my packed P columns
-        const uint32_t o_tmem = lane_base + NQ * kBlockN + q * D + part * kOCols;
-        float* xch = reinterpret_cast<float*>(smem_gen + L::kXchOff);            // [2][NQ][2][128] row exchange
-        const int n_q = n_tiles[q];
+        const uint32_t p_tmem = lane_base + T::kPOff + q * (kBlockN / 2);   // my packed P columns
+        const uint32_t o_tmem = lane_base + T::kOOff + q * D;
+        const int n_q = q == 0 ? n_tiles[0] : n_tiles[NQ - 1];
         const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
         const float sl2 = p.scale_log2;
         const uint64_t sl2_2 = pack_f2(sl2, sl2);
@@ -449,33 +486,28 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         bool ok = true;
 
         const bool probe = DBG == 5 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
-        long long pt_wait = 0, pt_max = 0, pt_exp = 0, pt0 = 0, pt1 = 0, pt2 = 0;
+        long long pt_wait = 0, pt_max = 0, pt_exp = 0, pt_pv = 0, pt0 = 0, pt1 = 0, pt2 = 0;
+        const bool tr = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
         for (int j = 0; j < (kFreeRun ? 0 : n_q) && ok; ++j) {
             if constexpr (DBG == 5) pt0 = clock64();
+            const int buf = s_buffer(q, j);
+            const uint32_t s_tmem = lane_base + T::kSOff + buf * kBlockN;
             ok = wait_barrier(bar_s_full(q), j & 1, p.error_flag, 7);
             tc_fence_after();
             if constexpr (DBG == 5) pt1 = clock64();
-            if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) {
-                    if (SPLIT == 1 || part == 0) mbar_arrive(bar_p_ready(q, 0));
-                    if (SPLIT == 1 || part == 1) mbar_arrive(bar_p_ready(q, 1));
-                }
-                continue;
-            }
+            trace_event(tr, q, j, 8);
             uint32_t su[kCols];
+            if constexpr (DBG != 2) {
 #pragma unroll
-            for (int c = 0; c < kCols / 2; c += 32) tmem_ld32(s_tmem + c, &su[c]);
-            tmem_wait_ld();
+                for (int c = 0; c < kCols / 2; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+                tmem_wait_ld();
 #pragma unroll
-            for (int c = kCols / 2; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
-
+                for (int c = kCols / 2; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+            }
             const int key0 = j * kBlockN;
             const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
                                    (key0 + kBlockN > p.seqlen_k);
-            // my columns <= lim stay (masked tiles only)
-            const int lim = min(key_limit, p.seqlen_k - 1) - key0 - part * kCols;
+            const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
             // ---- row maximum: four independent chains, first half while the second half is in flight
             float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
             auto scan_half = [&](int base) {
@@ -488,32 +520,50 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 for (int c = base; c < base + kCols / 2; c += 2)
                     mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
             };
-            scan_half(0);
+            if constexpr (DBG != 2) scan_half(0);
             tmem_wait_ld();
-            scan_half(kCols / 2);
-            float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-            if constexpr (SPLIT == 2) {
-                // The two threads of a row swap their partial maxima (double-buffered by tile parity).  The
-                // barrier also orders my partner's S loads before my P store into its columns.
-                float* slot = xch + (((j & 1) * NQ + q) * 2) * kBlockM;
-                slot[part * kBlockM + row_in_tile] = mx_all;
-                named_barrier_sync(1 + q, 256);
-                mx_all = fmaxf(mx_all, slot[(part ^ 1) * kBlockM + row_in_tile]);
+            // the scores are in registers: hand the buffer back so that the next Q.K runs under this softmax
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
+            trace_event(tr, q, j, 9);
+            if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
+                if (j > 0) ok = wait_barrier(bar_pv_done(q), (j - 1) & 1, p.error_flag, 8);
+                if (lane == 0) {
+                    mbar_arrive(bar_p_ready(q, 0));
+                    mbar_arrive(bar_p_ready(q, 1));
+                }
+                continue;
             }
+            scan_half(kCols / 2);
+            const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
 
+            // P(q, j-1) is still being read by the tensor pipe, and O(q) still accumulated into, until pv_done
+            bool pv_waited = j == 0;
+            auto wait_pv = [&]() {
+                if (!pv_waited) {
+                    long long c0 = 0;
+                    if constexpr (DBG == 5) c0 = clock64();
+                    ok = wait_barrier(bar_pv_done(q), (j - 1) & 1, p.error_flag, 8);
+                    tc_fence_after();
+                    pv_waited = true;
+                    if constexpr (DBG == 5) pt_pv += clock64() - c0;
+                }
+            };
             const float m_new = fmaxf(m_used, mx_all);
             if (j == 0) {
                 m_used = m_new;
             } else {
                 const bool grow = (m_new - m_used) * sl2 > kRescaleThreshold;   // false for -inf - -inf (NaN)
                 if (__any_sync(0xffffffffu, grow)) {
+                    wait_pv();
                     const float alpha = grow ? ex2((m_used - m_new) * sl2) : 1.f;
                     const uint64_t alpha2 = pack_f2(alpha, alpha);
                     l_acc[0] = fmul2(l_acc[0], alpha2);
                     l_acc[1] = fmul2(l_acc[1], alpha2);
                     if (grow) m_used = m_new;
 #pragma unroll
-                    for (int c = 0; c < kOCols / 16; ++c) {   // 16-column chunks: the scores stay in registers
+                    for (int c = 0; c < D / 16; ++c) {   // 16-column chunks: the scores stay in registers
                         uint32_t o[16];
                         tmem_ld16(o_tmem + 16 * c, o);
                         tmem_wait_ld();
@@ -526,6 +576,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
             const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
             if constexpr (DBG == 5) pt2 = clock64();
+            trace_event(tr, q, j, 10);
             // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
             // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
             auto exp_and_store = [&](auto poly_tag) {
@@ -553,7 +604,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     }
                     l_acc[i & 1] = fadd2_v(l_acc[i & 1], pack_f2(p0, p1));
                     pk[i & 31] = pack_pair<BF16>(p0, p1);
-                    if ((i & 31) == 31) tmem_st32(p_tmem + (i >> 5) * 32, pk);
+                    if ((i & 31) == 31) {
+                        if (i == 31) wait_pv();      // the previous tile's P.V must have drained before P is overwritten
+                        tmem_st32(p_tmem + (i >> 5) * 32, pk);
+                    }
                     // the hand-off of a 64-key block trails its store by a few pairs, so that the MUFU keeps
                     // running while the store drains (the last block has nothing left to overlap with)
                     constexpr int kTrail = 6;
@@ -562,9 +616,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) {
-                            if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, part * (kCols / 64) + (kPairs / 32 - 1)));
-                            else mbar_arrive(bar_p_ready(q, part * (kCols / 64) + (i >> 5) - 1));
+                            if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, kPairs / 32 - 1));
+                            else mbar_arrive(bar_p_ready(q, (i >> 5) - 1));
                         }
+                        trace_event(tr, q, j, i == kPairs - 1 ? 12 : 11);
                     }
                 }
             };
@@ -575,32 +630,27 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 pt_wait += pt1 - pt0; pt_max += pt2 - pt1; pt_exp += pt3 - pt2;
             }
         }
-        if (probe && part == 0) {
+        if (probe) {
             g_fwd_probe[8 * q + 0] = pt_wait; g_fwd_probe[8 * q + 1] = pt_max; g_fwd_probe[8 * q + 2] = pt_exp;
-            g_fwd_probe[8 * q + 3] = n_q;
+            g_fwd_probe[8 * q + 3] = n_q; g_fwd_probe[8 * q + 4] = pt_pv;
         }
 
         // ---- epilogue: O / l -> global, LSE
         float l0, l1, l2, l3;
         unpack_f2(l_acc[0], l0, l1);
         unpack_f2(l_acc[1], l2, l3);
-        float l_sum = (l0 + l1) + (l2 + l3);
-        if constexpr (SPLIT == 2) {
-            // both parity buffers are quiescent after one more barrier; use buffer 0 of this query tile
-            named_barrier_sync(1 + q, 256);
-            float* slot = xch + (q * 2) * kBlockM;
-            slot[part * kBlockM + row_in_tile] = l_sum;
-            named_barrier_sync(1 + q, 256);
-            l_sum += slot[(part ^ 1) * kBlockM + row_in_tile];
-        }
+        const float l_sum = (l0 + l1) + (l2 + l3);
         const bool row_ok = row < p.seqlen_q;
         const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
         uint8_t* o_row = reinterpret_cast<uint8_t*>(p.o) +
-                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs + part * kOCols);
-        if (n_q > 0 && ok) ok = wait_barrier(bar_o_final(q), 0, p.error_flag, 8);
+                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs);
+        if constexpr (kFreeRun) {   // probe: nobody followed the phases of pv_done, walk through all of them
+            for (int j = 0; j + 1 < n_q && ok; ++j) ok = wait_barrier(bar_pv_done(q), j & 1, p.error_flag, 10);
+        }
+        if (n_q > 0 && ok) ok = wait_barrier(bar_pv_done(q), (n_q - 1) & 1, p.error_flag, 10);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < kOCols / 32; ++c) {
+        for (int c = 0; c < D / 32; ++c) {
             uint32_t o[32];
             if (n_q > 0) {
                 tmem_ld32(o_tmem + 32 * c, o);
@@ -620,13 +670,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
             }
         }
-        if (row_ok && p.lse && part == 0) {
+        if (row_ok && p.lse) {
             const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
             p.lse[((int64_t)b * p.heads_q + h) * p.seqlen_q + row] = lse;
         }
-    }
-
-    else {
+    } else {
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warps of the third warpgroup
     }
 
@@ -635,7 +683,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     __syncthreads();
     if (warp == kSoftmaxWarps + 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
+        tmem_dealloc(tmem_base, T::kCols);
     }
 }
 
@@ -676,11 +724,11 @@ int make_map(CUtensorMap* map, const void* base, int dtype, int head_dim, int he
     return SFA_OK;
 }
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG, int SPLIT = 1>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
 int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p,
                     int batch, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG, SPLIT>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -689,56 +737,47 @@ int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensor
     SFA_CUDA_CHECK(attr_err);
     const int m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     dim3 grid(m_blocks, p.heads_q, batch);
-    kern<<<grid, FwdRegs<NQ, SPLIT>::kThreads, L::kAlloc, stream>>>(qm, km, vm, p);
+    kern<<<grid, FwdRegs<NQ>::kThreads, L::kAlloc, stream>>>(qm, km, vm, p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return SFA_OK;
 }
 
-// Host launcher: the tile configuration per (head_dim, rows, dtype).  kPolyDefault of every 8 column pairs
-// take the polynomial exp2 (the MUFU is co-critical with the tensor pipe at head_dim 128 and dominant at 64).
-constexpr int kSplitDefault = 1;
-
+// Host launcher: the tile configuration per (head_dim, rows, dtype) - what the reference's Traits<> template
+// (src/traits.h:7-26) selects at compile time.  Ring depth: as many 128-key tiles as fit beside the Q tiles.
 template <bool BF16>
 int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p, int batch,
                  int head_dim, int nq, cudaStream_t stream) {
-    // Tuning / probe overrides (tools/fwd_time.py): SFA_FWD_SPLIT in {1,2}, SFA_FWD_POLY in {0,2,3,4},
-    // SFA_FWD_DBG probes (bf16, head_dim 128, two query tiles only).
+    // Tuning / probe overrides (tools/fwd_time.py): SFA_FWD_POLY in {0,2,3}, SFA_FWD_DBG probes (bf16, head_dim 128
+    // and fp16, head_dim 64, two query tiles only), SFA_FWD_STAGES in {4,5} at head_dim 128.
     static const int poly = [] { const char* e = getenv("SFA_FWD_POLY"); return e ? atoi(e) : -1; }();
     static const int dbg = [] { const char* e = getenv("SFA_FWD_DBG"); return e ? atoi(e) : 0; }();
-    static const int split = [] { const char* e = getenv("SFA_FWD_SPLIT"); return e ? atoi(e) : kSplitDefault; }();
-#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DBG_, SPLIT_) \
-    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DBG_, SPLIT_>(qm, km, vm, p, batch, stream)
+    static const int stages = [] { const char* e = getenv("SFA_FWD_STAGES"); return e ? atoi(e) : 0; }();
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DBG_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DBG_>(qm, km, vm, p, batch, stream)
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 0, 1);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 0);
         if constexpr (BF16) {
-            if (split == 2) {
-                if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2, 2);
-                if (dbg == 5 && poly == 2) SFA_LAUNCH(128, 2, 4, 2, 5, 2);
-                if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5, 2);
-                if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0, 2);
-                if (poly == 3) SFA_LAUNCH(128, 2, 4, 3, 0, 2);
-                if (poly == 4) SFA_LAUNCH(128, 2, 4, 4, 0, 2);
-            } else {
-                if (dbg == 1) SFA_LAUNCH(128, 2, 4, 0, 1, 1);
-                if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2, 1);
-                if (dbg == 4) SFA_LAUNCH(128, 2, 4, 0, 4, 1);
-                if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5, 1);
-                if (dbg == 6) SFA_LAUNCH(128, 2, 4, 0, 6, 1);
-                if (dbg == 7) SFA_LAUNCH(128, 2, 4, 0, 7, 1);
-                if (dbg == 8) SFA_LAUNCH(128, 2, 4, 0, 8, 1);
-                if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0, 1);
-            }
+            if (dbg == 1) SFA_LAUNCH(128, 2, 4, 0, 1);
+            if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2);
+            if (dbg == 4) SFA_LAUNCH(128, 2, 4, 0, 4);
+            if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5);
+            if (dbg == 6) SFA_LAUNCH(128, 2, 4, 0, 6);
+            if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0);
+            if (poly == 3) SFA_LAUNCH(128, 2, 4, 3, 0);
+            if (stages == 5) SFA_LAUNCH(128, 2, 5, 0, 0);
         }
-        if (split == 2) SFA_LAUNCH(128, 2, 4, 0, 0, 2);
-        SFA_LAUNCH(128, 2, 4, 0, 0, 1);
+        SFA_LAUNCH(128, 2, 4, 0, 0);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, 1);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0);
     if constexpr (!BF16) {
-        if (split == 2 && poly == 3) SFA_LAUNCH(64, 2, 6, 3, 0, 2);
+        if (dbg == 5) SFA_LAUNCH(64, 2, 6, 0, 5);
+        if (poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0);
+        if (poly == 4) SFA_LAUNCH(64, 2, 6, 4, 0);
     }
-    if (split == 2) SFA_LAUNCH(64, 2, 6, 0, 0, 2);
-    SFA_LAUNCH(64, 2, 6, 0, 0, 1);
+    // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
+    // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
+    SFA_LAUNCH(64, 2, 6, 2, 0);
 #undef SFA_LAUNCH
 }
 
@@ -749,7 +788,7 @@ int fwd_error_flag_read(int* value) {
     return SFA_OK;
 }
 int fwd_probe_read(unsigned long long* out, int n) {
-    if (n > 32) n = 32;
+    if (n > 32 + 2048) n = 32 + 2048;
     SFA_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_fwd_probe, n * sizeof(unsigned long long)));
     return SFA_OK;
 }

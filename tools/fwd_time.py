@@ -61,7 +61,7 @@ def main():
                f"{statistics.median(half):.0f} MHz min {min(sm)} max {max(sm)}, power max {max(pw):.0f} W")
     except Exception as e:  # noqa: BLE001
         clk = f" | clock sampling failed: {e!r}"
-    if os.environ.get("SFA_FWD_DBG") in ("4", "5", "6", "7", "8"):
+    if os.environ.get("SFA_FWD_DBG") in ("4", "5"):
         import ctypes
         from starflashattention_b200 import _capi
         buf = (ctypes.c_uint64 * 32)()
@@ -69,10 +69,11 @@ def main():
         v_ = list(buf)
         for qq in (0, 1):
             n = max(1, v_[8 * qq + 3])
-            print(f"[probe] softmax q{qq}: tiles {n}  per tile: wait S {v_[8*qq]/n:.0f}  ld+max {v_[8*qq+1]/n:.0f}  exp+store {v_[8*qq+2]/n:.0f} cycles")
+            print(f"[probe] softmax q{qq}: tiles {n}  per tile: wait S {v_[8*qq]/n:.0f}  ld+max {v_[8*qq+1]/n:.0f}  "
+                  f"exp+store {v_[8*qq+2]/n:.0f} (of which wait PV {v_[8*qq+4]/n:.0f}) cycles")
         n = max(1, v_[20])
-        print(f"[probe] mma warp: iters {n}  per iter: wait P0 {v_[16]/n:.0f}  wait P1 {v_[17]/n:.0f}  wait KV {v_[18]/n:.0f}  total {v_[19]/n:.0f} cycles")
-    print(f"[fwd_time] {name} POLY={os.environ.get('SFA_FWD_POLY','-')} DBG={os.environ.get('SFA_FWD_DBG','-')} "
+        print(f"[probe] mma warp: iters {n}  per iter: wait P {v_[16]/n:.0f}  wait S-free {v_[17]/n:.0f}  wait KV {v_[18]/n:.0f}  total {v_[19]/n:.0f} cycles")
+    print(f"[fwd_time] {name} POLY={os.environ.get('SFA_FWD_POLY','-')} DBG={os.environ.get('SFA_FWD_DBG','-')} STAGES={os.environ.get('SFA_FWD_STAGES','-')} "
           f"median {ms:.3f} ms  min {min(ts):.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s (median)  watchdog={wd}{clk}", flush=True)
 
 
