@@ -23,10 +23,15 @@ int resolve_splits(int requested, int batch, int heads_kv, int max_len, int sm_c
     return choose_decode_splits(batch, heads_kv, max_len, sm_count);
 }
 
-int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream) {
+struct FusedStep {   // new-token inputs of the fused decoder step (see DecodeLaunch)
+    const void* qkv; const void* cos_table; const void* sin_table;
+    int64_t qkv_stride; int rotary_dim;
+};
+
+int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream, const FusedStep* fused = nullptr) {
     int rc = check_dtype(a.dtype);
     if (rc) return rc;
-    if (!a.q || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "decode: null tensor pointer");
+    if ((!a.q && !fused) || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "decode: null tensor pointer");
     if (a.batch < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0)
         return fail(SFA_ERR_INVALID, "decode: negative or zero dimension");
     if (a.heads_q % a.heads_kv) return fail(SFA_ERR_INVALID, "decode: heads_q must be a multiple of heads_kv");
@@ -53,6 +58,10 @@ int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream) {
     L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv, a.seqlen_k + seqlen_add, dev->sm_count);
     L.dtype = a.dtype;
     L.o_part = nullptr; L.ml_part = nullptr;
+    if (fused) {
+        L.fused_qkv = fused->qkv; L.cos_table = fused->cos_table; L.sin_table = fused->sin_table;
+        L.qkv_stride = fused->qkv_stride; L.rotary_dim = fused->rotary_dim;
+    }
     if (L.num_splits > 1) {
         const size_t need = decode_workspace_bytes(a.batch, a.heads_q, a.head_dim, L.num_splits);
         uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
@@ -86,23 +95,36 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     if (!dev) return SFA_ERR_NO_DEVICE;
 
     const int B = a.batch_size, H = a.num_heads, D = a.head_dim;
+    if (a.rotary_embedding_dim % 2 || a.rotary_embedding_dim > D || a.rotary_embedding_dim < 0)
+        return fail(SFA_ERR_INVALID, "rotary_embedding_dim must be even and <= head_dim");
+    if ((a.rotary_cos_table == nullptr) != (a.rotary_sin_table == nullptr))
+        return fail(SFA_ERR_INVALID, "rotary cos and sin tables must be given together");
+    // One kernel (RoPE + append inside the split-KV kernel) unless SFA_DECODER_FUSED=0 asks for the three-launch
+    // form (stand-alone RoPE/append kernel first), kept for A/B checks.
+    const char* fused_env = getenv("SFA_DECODER_FUSED");   // read per call: the GPU tests flip it
+    const bool fused = !(fused_env && atoi(fused_env) == 0);
     const int splits = resolve_splits(a.num_splits, B, H, a.memory_max_len, dev->sm_count);
-    const size_t q_bytes = align_up((size_t)B * H * D * 2, 256);
+    const size_t q_bytes = fused ? 0 : align_up((size_t)B * H * D * 2, 256);
     const size_t part_bytes = decode_workspace_bytes(B, H, D, splits);
-    uint8_t* ws = reinterpret_cast<uint8_t*>(get_workspace(q_bytes + part_bytes, stream));
-    if (!ws) return SFA_ERR_CUDA;
+    uint8_t* ws = nullptr;
+    if (q_bytes + part_bytes) {
+        ws = reinterpret_cast<uint8_t*>(get_workspace(q_bytes + part_bytes, stream));
+        if (!ws) return SFA_ERR_CUDA;
+    }
 
-    RopeAppendLaunch R;
-    R.qkv = a.qkv; R.qkv_stride = a.qkv_stride; R.q_rot = ws;
-    R.k_cache = a.k_cache_table; R.v_cache = a.v_cache_table; R.seq_len = a.seq_len;
-    R.cos_table = a.rotary_cos_table; R.sin_table = a.rotary_sin_table;
-    R.batch = B; R.heads = H; R.head_dim = D; R.rotary_dim = a.rotary_embedding_dim; R.max_len = a.memory_max_len;
-    R.num_layer = a.num_layer; R.idx_layer = a.idx_layer; R.dtype = a.dtype;
-    if ((rc = launch_rope_append(R, stream))) return rc;
+    if (!fused) {
+        RopeAppendLaunch R;
+        R.qkv = a.qkv; R.qkv_stride = a.qkv_stride; R.q_rot = ws;
+        R.k_cache = a.k_cache_table; R.v_cache = a.v_cache_table; R.seq_len = a.seq_len;
+        R.cos_table = a.rotary_cos_table; R.sin_table = a.rotary_sin_table;
+        R.batch = B; R.heads = H; R.head_dim = D; R.rotary_dim = a.rotary_embedding_dim; R.max_len = a.memory_max_len;
+        R.num_layer = a.num_layer; R.idx_layer = a.idx_layer; R.dtype = a.dtype;
+        if ((rc = launch_rope_append(R, stream))) return rc;
+    }
 
     const int64_t layer_elems = (int64_t)a.memory_max_len * H * D;
     sfa_decode_args d = {};
-    d.q = ws;
+    d.q = fused ? nullptr : ws;
     d.k_cache = reinterpret_cast<const uint8_t*>(a.k_cache_table) + 2 * layer_elems * a.idx_layer;
     d.v_cache = reinterpret_cast<const uint8_t*>(a.v_cache_table) + 2 * layer_elems * a.idx_layer;
     d.seqlens = a.seq_len; d.o = a.o; d.lse = a.lse;
@@ -114,7 +136,10 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     d.softmax_scale = a.head_dim_inv;
     d.num_splits = splits; d.dtype = a.dtype;
     d.workspace = part_bytes ? ws + q_bytes : nullptr; d.workspace_bytes = part_bytes;
-    return decode_impl(d, /*seqlen_add=*/1, stream);
+    if (!fused) return decode_impl(d, /*seqlen_add=*/1, stream);
+    if ((uintptr_t)a.qkv % 16) return fail(SFA_ERR_INVALID, "decoder step: qkv must be 16-byte aligned");
+    const FusedStep f = {a.qkv, a.rotary_cos_table, a.rotary_sin_table, a.qkv_stride, a.rotary_embedding_dim};
+    return decode_impl(d, /*seqlen_add=*/1, stream, &f);
 }
 
 }  // namespace

@@ -1,8 +1,11 @@
 // Split-KV decode attention (one query token per sequence) for sm_100a.
 //
 // Replaces the reference's flash_decoder_kernel / flash_combine_kernel pair
-// (reference src/flash_attn.cu:554-875 and :877-935) without the RoPE/append prologue, extended to
-// GQA, bf16, ragged sequence lengths and an LSE output.  HBM-bound: every K and V byte is read
+// (reference src/flash_attn.cu:554-875 and :877-935), extended to GQA, bf16, ragged sequence lengths and
+// an LSE output.  The FUSED instantiation is the reference's whole decoder step in one kernel, as its
+// flash_decoder_kernel intends (:591-601 q/k RoPE at position seq_len[b], :696-701 cache append): the new
+// token's q, k, v are read from the packed qkv row, q and k are rotated in registers, and the one warp whose
+// 16-key step holds the appended position feeds its fragments from qkv and writes k, v to the cache.  HBM-bound: every K and V byte is read
 // exactly once, straight from global memory into tensor-core fragments, so there is no shared
 // memory staging on the streaming path at all.
 //
@@ -17,8 +20,10 @@
 // each thread's K fragment is one contiguous 16-byte load, and the output head_dim axis of P.V is
 // permuted such that each thread's V fragment comes from 16-byte loads too (two PRMTs per MMA).
 #include "internal.h"
+#include "rope.cuh"
 
 #include <math.h>
+#include <type_traits>
 
 namespace sfa {
 namespace {
@@ -83,6 +88,13 @@ struct DecodeParams {
     int64_t q_bs, q_hs, k_bs, k_rs, k_hs, v_bs, v_rs, v_hs, o_bs, o_hs;
     int seqlen_k, seqlen_add, heads_q, group, num_splits;
     float scale_log2;
+    // fused decoder step (FUSED kernels only): the new token's q/k/v come from `qkv`, q and k are rotated at
+    // position seqlens[b], and the CTA whose chunk ends at that position appends k, v to the cache
+    const void* qkv;
+    const void* cos_table;
+    const void* sin_table;
+    int64_t qkv_stride;
+    int rotary_dim, heads_kv;
 };
 
 // Shared memory used only for the end-of-CTA merge of the four warp states.
@@ -93,7 +105,7 @@ struct MergeSmem {
     float l[kWarps][8];
 };
 
-template <typename T, int D>
+template <typename T, int D, bool FUSED>
 __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const DecodeParams p) {
     constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
     constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
@@ -104,21 +116,38 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
     const int r = lane >> 2, t = lane & 3;
     const int g = p.group;
 
-    int len = (p.seqlens ? p.seqlens[b] : p.seqlen_k) + p.seqlen_add;
+    const int pos = p.seqlens ? p.seqlens[b] : p.seqlen_k;   // FUSED: row the new token is appended at
+    int len = pos + p.seqlen_add;
     len = max(0, min(len, p.seqlen_k + p.seqlen_add));   // never read past the cache
+    // FUSED: the appended token exists only while the cache has room (as in the stand-alone append kernel)
+    const bool has_new = FUSED && pos >= 0 && pos < p.seqlen_k + p.seqlen_add;
     // Per-sequence chunking keeps ragged batches balanced across the splits.
     const int chunk = (((len + p.num_splits - 1) / p.num_splits) + 63) & ~63;
     const int k_begin = split * chunk;
     const int k_end = min(len, k_begin + chunk);
 
+    // The new token of the fused step: (q | k | v) planes of heads_q, heads_kv, heads_kv heads.  Its 16-key
+    // step is the last one of the last non-empty split; that step is peeled off the streaming loop so that
+    // the loop itself is the plain decode loop (no extra live registers, no extra branch).
+    const int new_base = k_begin + ((pos - k_begin) & ~(kStepKeys - 1));
+    const bool cta_has_new = has_new && pos >= k_begin && pos < k_end;
+    const int k_end_main = cta_has_new ? new_base : k_end;
+    auto token_row = [&](int plane_head) {   // element pointer of head `plane_head` of the packed qkv row
+        return reinterpret_cast<const T*>(p.qkv) + (int64_t)b * p.qkv_stride + (int64_t)plane_head * D;
+    };
+
     // ---- query fragments (A operand), rows >= g are zero padding
     uint32_t qa[NJ][4];
     {
-        const T* qrow = reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_bs + (int64_t)(hk * g + r) * p.q_hs;
+        const T* qrow = FUSED ? token_row(hk * g + r)
+                              : reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_bs + (int64_t)(hk * g + r) * p.q_hs;
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             uint4 w = make_uint4(0, 0, 0, 0);
-            if (r < g) w = *reinterpret_cast<const uint4*>(qrow + 32 * j + 8 * t);
+            if (r < g) {
+                w = *reinterpret_cast<const uint4*>(qrow + 32 * j + 8 * t);
+                if constexpr (FUSED) w = rope_rotate8<T>(w, 32 * j + 8 * t, pos, p.rotary_dim, p.cos_table, p.sin_table);
+            }
             qa[j][0] = w.x; qa[j][1] = w.y; qa[j][2] = w.z; qa[j][3] = w.w;
         }
     }
@@ -132,24 +161,51 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
     const T* kbase = reinterpret_cast<const T*>(p.k) + (int64_t)b * p.k_bs + (int64_t)hk * p.k_hs;
     const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)b * p.v_bs + (int64_t)hk * p.v_hs;
 
-    for (int base = k_begin + warp * kStepKeys; base < k_end; base += kWarps * kStepKeys) {
+    T* kcache = const_cast<T*>(kbase);   // FUSED: the cache is appended to
+    T* vcache = const_cast<T*>(vbase);
+    // One 16-key step of this warp.  NEW (fused step only): the step holds the appended token, whose k (rotated
+    // here) and v come from `qkv` instead of the cache and are written to the cache row `pos` by the threads
+    // whose fragment is that row.
+    auto step = [&](const int base, auto new_tag) {
+        constexpr bool NEW = decltype(new_tag)::value;
         const int last = k_end - 1;
+        const T* tok_k = NEW ? token_row(p.heads_q + hk) : nullptr;
+        const T* tok_v = NEW ? token_row(p.heads_q + p.heads_kv + hk) : nullptr;
         // ---- issue every load of the step up front (16 x 16 B per thread at D=128)
         uint4 kf[2][NJ];
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
             const int key = min(base + 8 * nt + r, last);
-            const T* row = kbase + (int64_t)key * p.k_rs + 8 * t;
+            const bool from_tok = NEW && key == pos;
+            const T* row = (from_tok ? tok_k : kbase + (int64_t)key * p.k_rs) + 8 * t;
 #pragma unroll
             for (int j = 0; j < NJ; ++j) kf[nt][j] = ld_stream(row + 32 * j);
+            if constexpr (NEW) {
+                if (from_tok) {
+#pragma unroll
+                    for (int j = 0; j < NJ; ++j) {
+                        kf[nt][j] = rope_rotate8<T>(kf[nt][j], 32 * j + 8 * t, pos, p.rotary_dim, p.cos_table, p.sin_table);
+                        if (base + 8 * nt + r == pos)   // the unclamped owner of the row appends it
+                            *reinterpret_cast<uint4*>(kcache + (int64_t)pos * p.k_rs + 32 * j + 8 * t) = kf[nt][j];
+                    }
+                }
+            }
         }
         uint4 vf[4][NH];
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) {
-            const int key = min(base + 2 * t + (kk & 1) + 8 * (kk >> 1), last);
-            const T* row = vbase + (int64_t)key * p.v_rs + 8 * r;
+            const int key_raw = base + 2 * t + (kk & 1) + 8 * (kk >> 1);
+            const int key = min(key_raw, last);
+            const bool from_tok = NEW && key == pos;
+            const T* row = (from_tok ? tok_v : vbase + (int64_t)key * p.v_rs) + 8 * r;
 #pragma unroll
-            for (int h = 0; h < NH; ++h) vf[kk][h] = ld_stream(row + 64 * h);
+            for (int h = 0; h < NH; ++h) {
+                vf[kk][h] = ld_stream(row + 64 * h);
+                if constexpr (NEW) {
+                    if (from_tok && key_raw == pos)
+                        *reinterpret_cast<uint4*>(vcache + (int64_t)pos * p.v_rs + 8 * r + 64 * h) = vf[kk][h];
+                }
+            }
         }
 
         // ---- S = Q K^T for two 8-key tiles
@@ -204,6 +260,11 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
                 const uint32_t b1 = __byte_perm(u4_word(vf[2][h], i >> 1), u4_word(vf[3][h], i >> 1), sel);
                 mma_16816<T>(o_acc[h * 8 + i], pa0, 0u, pa2, 0u, b0, b1);
             }
+    };
+    for (int base = k_begin + warp * kStepKeys; base < k_end_main; base += kWarps * kStepKeys)
+        step(base, std::false_type{});
+    if constexpr (FUSED) {
+        if (cta_has_new && warp == ((new_base - k_begin) / kStepKeys) % kWarps) step(new_base, std::true_type{});
     }
 
     // ---- merge the four warp states
@@ -277,7 +338,8 @@ __global__ void __launch_bounds__(D) decode_combine_kernel(const DecodeParams p)
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
     dim3 grid(a.num_splits, a.heads_kv, a.batch);
-    decode_splitkv_kernel<T, D><<<grid, kWarps * 32, 0, stream>>>(p);
+    if (a.fused_qkv) decode_splitkv_kernel<T, D, true><<<grid, kWarps * 32, 0, stream>>>(p);
+    else decode_splitkv_kernel<T, D, false><<<grid, kWarps * 32, 0, stream>>>(p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     if (a.num_splits > 1) {
@@ -329,6 +391,8 @@ int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     p.seqlen_k = a.seqlen_k; p.seqlen_add = a.seqlen_add; p.heads_q = a.heads_q; p.group = g;
     p.num_splits = a.num_splits;
     p.scale_log2 = a.scale * kLog2e;
+    p.qkv = a.fused_qkv; p.cos_table = a.cos_table; p.sin_table = a.sin_table; p.qkv_stride = a.qkv_stride;
+    p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv;
     if (a.dtype == SFA_FP16) {
         return a.head_dim == 128 ? launch_typed<__half, 128>(a, p, stream) : launch_typed<__half, 64>(a, p, stream);
     }

@@ -46,6 +46,13 @@ struct DecodeLaunch {
     float* o_part;           // (B,Hq,S,D) fp32   (unused when num_splits == 1)
     float2* ml_part;         // (B,Hq,S)  (m in log2 domain, l)
     int dtype;
+    // Fused decoder step (nullptr = plain decode): q/k/v of the new token are read from fused_qkv
+    // ((batch, heads_q + 2 heads_kv, head_dim) rows of qkv_stride elements), q and k are rotated at position
+    // seqlens[b] and k, v are appended to the cache row seqlens[b] by the decode kernel itself.
+    const void* fused_qkv = nullptr;
+    const void* cos_table = nullptr; const void* sin_table = nullptr;
+    int64_t qkv_stride = 0;
+    int rotary_dim = 0;
 };
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count);
 size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits);

@@ -6,33 +6,10 @@
 // init_half_array_kernel / init_half_array :493-510.  Cache layout is the documented
 // (batch, num_layer, memory_max_len, heads, head_dim) of src/params.h:22-25.
 #include "internal.h"
+#include "rope.cuh"
 
 namespace sfa {
 namespace {
-
-template <typename T> struct Vec2;
-template <> struct Vec2<__half> {
-    using type = __half2;
-    static __device__ float2 to_f(type v) { return __half22float2(v); }
-    static __device__ type from_f(float a, float b) { return __floats2half2_rn(a, b); }
-    static __device__ float one_to_f(__half v) { return __half2float(v); }
-    static __device__ __half one_from_f(float v) { return __float2half_rn(v); }
-};
-template <> struct Vec2<__nv_bfloat16> {
-    using type = __nv_bfloat162;
-    static __device__ float2 to_f(type v) { return __bfloat1622float2(v); }
-    static __device__ type from_f(float a, float b) { return __floats2bfloat162_rn(a, b); }
-    static __device__ float one_to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
-    static __device__ __nv_bfloat16 one_from_f(float v) { return __float2bfloat16_rn(v); }
-};
-
-// angle_i(pos) = pos * fl32(10000^(-2i/rot_dim)); the inverse frequency is rounded once from
-// double so it is the correctly rounded fp32 value, the product is an fp32 multiply as in the
-// Python example (examples/python/testFlashDecoder.py:10,20-25).
-__device__ __forceinline__ float rope_angle(int pos, int pair, int rot_dim) {
-    const float inv_freq = (float)(1.0 / pow(10000.0, (double)(2 * pair) / (double)rot_dim));
-    return (float)pos * inv_freq;
-}
 
 struct RopeParams {
     const void* qkv;
@@ -62,13 +39,7 @@ __global__ void rope_append_kernel(const RopeParams p) {
     const T2 v = *reinterpret_cast<const T2*>(tok + 2 * plane + hd);
     if (2 * i < p.rotary_dim) {
         float c, s;
-        if (p.cos_table) {
-            const int64_t ti = (int64_t)pos * (p.rotary_dim / 2) + i;
-            c = V::one_to_f(reinterpret_cast<const T*>(p.cos_table)[ti]);
-            s = V::one_to_f(reinterpret_cast<const T*>(p.sin_table)[ti]);
-        } else {
-            sincosf(rope_angle(pos, i, p.rotary_dim), &s, &c);
-        }
+        rope_cos_sin<T>(p.cos_table, p.sin_table, pos, i, p.rotary_dim, c, s);
         q = make_float2(q.x * c - q.y * s, q.y * c + q.x * s);
         k = make_float2(k.x * c - k.y * s, k.y * c + k.x * s);
     }

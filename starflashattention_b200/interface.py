@@ -20,7 +20,7 @@ import torch
 from . import _capi
 from ._capi import DecodeArgs, DecoderStepArgs, FwdArgs, check, lib
 
-__all__ = ["fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
+__all__ = ["DecoderStepGraph", "fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
            "launch_count", "decode_num_splits"]
 
 
@@ -193,6 +193,58 @@ def mha_fwd_cuda(qkv: torch.Tensor, q_bias, k_bias, v_bias, k_cache_table: torch
     with torch.cuda.device(dev):
         check(lib.sfa_decoder_step(a, _stream()))
     return o
+
+
+class DecoderStepGraph:
+    """A whole decoder step (every layer's fused RoPE + append + split-KV attention + combine) captured once in a
+    CUDA graph and replayed per token: the reference pays 7 cudaMallocs, 3 blocking copies and a device
+    synchronise per call (src/flash_attn.cu:947-991); here a token costs one graph launch.
+
+    The graph reads ``qkv`` (num_layer, batch, 3, heads, head_dim) and ``seq_len`` (batch) and writes ``o``
+    (num_layer, batch, heads, head_dim); these are the instance's own static tensors - copy a token's
+    projections into ``qkv`` and call :meth:`step`, which also advances ``seq_len`` on the device.
+    (In a real model layer l's qkv depends on layer l-1's output; the projections between the attention calls
+    would be captured in the same graph by the caller.  This class covers the attention path this library owns.)"""
+
+    def __init__(self, k_cache_table: torch.Tensor, v_cache_table: torch.Tensor, seq_len: torch.Tensor, *,
+                 rotary_embedding_dim: Optional[int] = None, rotary_cos_table: Optional[torch.Tensor] = None,
+                 rotary_sin_table: Optional[torch.Tensor] = None, num_splits: int = 0):
+        B, L, M, H, D = k_cache_table.shape
+        dev = k_cache_table.device
+        self.k_cache_table, self.v_cache_table = k_cache_table, v_cache_table
+        self.seq_len = seq_len.to(device=dev, dtype=torch.int32).clone()
+        self.qkv = torch.zeros((L, B, 3, H, D), dtype=k_cache_table.dtype, device=dev)
+        self.o = torch.empty((L, B, H, D), dtype=k_cache_table.dtype, device=dev)
+        self.lse = torch.empty((L, B, H), dtype=torch.float32, device=dev)
+        rot = D if rotary_embedding_dim is None else rotary_embedding_dim
+
+        def run():
+            for layer in range(L):
+                mha_fwd_cuda(self.qkv[layer], None, None, None, k_cache_table, v_cache_table, self.seq_len,
+                             self.o[layer], B, M, H, D, rot, M, L, layer, rotary_cos_table=rotary_cos_table,
+                             rotary_sin_table=rotary_sin_table, lse=self.lse[layer], num_splits=num_splits)
+            self.seq_len.add_(1)
+
+        # Warm up on a side stream (grows the library's workspace outside capture), then roll the state back.
+        k0, v0, s0 = k_cache_table.clone(), v_cache_table.clone(), self.seq_len.clone()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            run()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        k_cache_table.copy_(k0); v_cache_table.copy_(v0); self.seq_len.copy_(s0)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            run()
+        k_cache_table.copy_(k0); v_cache_table.copy_(v0); self.seq_len.copy_(s0)
+        self.launches_per_step = L * (2 if decode_num_splits(B, M, H, dev) > 1 or num_splits > 1 else 1)
+
+    def step(self, qkv: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Replays the captured step on the current stream; returns the static output tensor."""
+        if qkv is not None:
+            self.qkv.copy_(qkv, non_blocking=True)
+        self.graph.replay()
+        return self.o
 
 
 def compute_rotary_table(max_seq_len: int, rot_embed_dim: int, dtype=torch.float16, device="cuda"):

@@ -204,6 +204,85 @@ def test_decoder_step_ragged_positions_and_cache_append(dtype, use_tables):
         assert torch.equal(kc_d[b, 1 - layer].cpu(), kc[b, 1 - layer])
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("D", [64, 128])
+def test_decoder_step_fused_equals_three_launch_form(dtype, D, monkeypatch):
+    """RoPE + append inside the split-KV kernel (default) against the stand-alone RoPE/append kernel followed by
+    the plain decode kernel (SFA_DECODER_FUSED=0): same arithmetic, so outputs and caches must be bit-identical.
+    Positions cover an empty cache, a step boundary (16 keys per warp step), a chunk boundary and a full cache."""
+    import starflashattention_b200 as sfa
+    B, L, M, H, layer = 6, 2, 1024, 4, 0
+    qkv = _rand((B, 3, H, D), dtype, 41)
+    kc = _rand((B, L, M, H, D), dtype, 42)
+    vc = _rand((B, L, M, H, D), dtype, 43)
+    seq = torch.tensor([0, 15, 16, 511, 777, 1023], dtype=torch.int32)
+    cos, sin = sfa.compute_rotary_table(M, D, dtype=dtype)
+    outs = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("SFA_DECODER_FUSED", fused)
+        kc_d, vc_d = kc.cuda(), vc.cuda()
+        o = torch.empty(B, H, D, dtype=dtype, device="cuda")
+        lse = torch.empty(B, H, dtype=torch.float32, device="cuda")
+        n0 = sfa.launch_count()
+        sfa.mha_fwd_cuda(qkv.cuda(), None, None, None, kc_d, vc_d, seq.cuda(), o, B, M, H, D, D, M, L, layer,
+                         rotary_cos_table=cos, rotary_sin_table=sin, lse=lse, num_splits=4)
+        torch.cuda.synchronize()
+        outs.append((o.cpu(), lse.cpu(), kc_d.cpu(), vc_d.cpu(), sfa.launch_count() - n0))
+    (o1, l1, k1, v1, n1), (o0, l0, k0, v0, n0_) = outs
+    assert n1 == 2 and n0_ == 3            # fused: split-KV + combine; unfused: RoPE/append + split-KV + combine
+    assert torch.equal(k1, k0) and torch.equal(v1, v0)
+    assert torch.equal(o1, o0) and torch.equal(l1, l0)
+
+
+def test_decoder_step_cache_full_does_not_append():
+    """seq_len == memory_max_len: no room for the token - nothing is written, attention runs over the full cache."""
+    import starflashattention_b200 as sfa
+    B, L, M, H, D = 1, 1, 256, 2, 128
+    qkv = _rand((B, 3, H, D), torch.float16, 51)
+    kc = _rand((B, L, M, H, D), torch.float16, 52)
+    vc = _rand((B, L, M, H, D), torch.float16, 53)
+    kc_d, vc_d = kc.cuda(), vc.cuda()
+    o = torch.empty(B, H, D, dtype=torch.float16, device="cuda")
+    sfa.mha_fwd_cuda(qkv.cuda(), None, None, None, kc_d, vc_d, torch.tensor([M], dtype=torch.int32).cuda(), o,
+                     B, M, H, D, D, M, L, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(kc_d.cpu(), kc) and torch.equal(vc_d.cpu(), vc)
+    assert bool(torch.isfinite(o.float()).all())
+
+
+def test_decoder_step_graph_replay_matches_eager_steps():
+    """Eight tokens through a two-layer captured decoder step (one graph launch per token) against the same
+    tokens through eager calls: identical outputs and caches; the sequence lengths advance on the device."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    B, L, M, H, D, steps = 2, 2, 512, 8, 128, 8
+    kc = _rand((B, L, M, H, D), dtype, 61)
+    vc = _rand((B, L, M, H, D), dtype, 62)
+    seq0 = torch.tensor([100, 37], dtype=torch.int32)
+    toks = [_rand((L, B, 3, H, D), dtype, 70 + i).cuda() for i in range(steps)]
+    # eager
+    kc_e, vc_e, seq_e = kc.cuda(), vc.cuda(), seq0.cuda()
+    outs_e = []
+    for t in toks:
+        o = torch.empty(L, B, H, D, dtype=dtype, device="cuda")
+        for layer in range(L):
+            sfa.mha_fwd_cuda(t[layer], None, None, None, kc_e, vc_e, seq_e, o[layer], B, M, H, D, D, M, L, layer)
+        seq_e += 1
+        outs_e.append(o.clone())
+    # captured
+    kc_g, vc_g = kc.cuda(), vc.cuda()
+    g = sfa.DecoderStepGraph(kc_g, vc_g, seq0.cuda())
+    assert torch.equal(kc_g.cpu(), kc) and torch.equal(vc_g.cpu(), vc)      # capture left the caches untouched
+    n0 = sfa.launch_count()
+    for t, o_e in zip(toks, outs_e):
+        o = g.step(t)
+        torch.cuda.synchronize()
+        assert torch.equal(o.cpu(), o_e.cpu())
+    assert sfa.launch_count() == n0            # replays launch through the graph, not through the library's host code
+    assert torch.equal(g.seq_len.cpu(), seq0 + steps)
+    assert torch.equal(kc_g.cpu(), kc_e.cpu()) and torch.equal(vc_g.cpu(), vc_e.cpu())
+
+
 def test_rotary_table_and_fill():
     import starflashattention_b200 as sfa
     M, D = 2048, 128
