@@ -100,6 +100,40 @@ int sfa_decode(const sfa_decode_args* args, void* stream);
 int sfa_decode_num_splits(const sfa_decode_args* args);
 size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits);
 
+/* ---------------------------------------------------------------- cross-GPU split-KV decode ---
+ * One long sequence whose KV length is sharded over the GPUs of a box (one process per GPU).  Every rank
+ * calls sfa_decode_sharded with ITS shard as k_cache/v_cache (seqlen_k = shard length, seqlens = number of
+ * visible keys inside the shard) and the same q; the split-KV kernel runs over the shard, then one kernel
+ * merges the rank's splits, stores (O_r, LSE_r) into every peer's workspace over NVLink (P2P stores into
+ * CUDA-IPC mapped buffers), waits for the peers' rows and merges them: every rank ends with the full O, LSE.
+ * No reference counterpart (the reference is single-GPU); the merge is flash_combine_kernel's
+ * (src/flash_attn.cu:877-935) applied across devices.
+ *   mode 0: fused peer exchange (needs peer_ws[0..world), peer_ws[rank] = own workspace from sfa_peer_alloc,
+ *           the others from sfa_peer_open; `step` must increase by one per call, starting at 1).
+ *   mode 1: publish only: (rows, head_dim + 1) fp32 to `payload` (rows = batch * heads_q; O rows, then the
+ *           LSEs in log2 units) for an external all-gather, to be merged by sfa_shard_merge. */
+typedef struct sfa_shard_comm {
+    int32_t rank, world;
+    uint32_t step;
+    int32_t mode;
+    void* peer_ws[8];
+    float* payload;
+} sfa_shard_comm;
+
+int sfa_decode_sharded(const sfa_decode_args* local_args, const sfa_shard_comm* comm, void* stream);
+/* Merges `world` gathered payloads laid out (world, rows, head_dim + 1) into o / lse. */
+int sfa_shard_merge(const float* payloads, int32_t world, void* o, float* lse, int32_t batch, int32_t heads_q,
+                    int32_t head_dim, int64_t o_batch_stride, int64_t o_head_stride, int32_t dtype, void* stream);
+size_t sfa_shard_workspace_bytes(int32_t world, int32_t batch, int32_t heads_q, int32_t head_dim);
+/* Peer-visible device buffer: cudaMalloc + zero fill + CUDA IPC handle (64 bytes) to pass to the other
+ * processes, which map it with sfa_peer_open.  Close mappings before the owner frees the buffer. */
+int sfa_peer_alloc(size_t bytes, void** ptr, uint8_t handle[64]);
+int sfa_peer_open(const uint8_t handle[64], void** ptr);
+int sfa_peer_close(void* ptr);
+int sfa_peer_free(void* ptr);
+/* Non-zero after a rank waited more than 2 s for a peer's rows (1 + the missing rank); synchronises. */
+int sfa_shard_watchdog(int clear);
+
 /* ---------------------------------------------------------------- drop-in decoder step -----
  * The reference's run_flash_decoder with plain arguments.  For every sequence b:
  * rotate q and k of the new token (interleaved pairs, position seq_len[b]) over the first

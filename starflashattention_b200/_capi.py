@@ -19,6 +19,8 @@ EXPORTED_SYMBOLS = (
     "sfa_fwd", "sfa_decode", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
+    "sfa_decode_sharded", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
+    "sfa_peer_close", "sfa_peer_free", "sfa_shard_watchdog",
 )
 # C++-mangled drop-ins of the reference's src/flash_attn.h:7-11.
 MANGLED_DROP_INS = (
@@ -68,6 +70,13 @@ class DecoderStepArgs(C.Structure):
     ]
 
 
+class ShardComm(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32), ("step", C.c_uint32), ("mode", C.c_int32),
+        ("peer_ws", C.c_void_p * 8), ("payload", C.c_void_p),
+    ]
+
+
 class StarFlashAttentionError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"libStarFlashAttention error {code}: {message}")
@@ -102,6 +111,23 @@ def _load() -> C.CDLL:
     lib.sfa_fwd_probe_read.argtypes = [C.POINTER(C.c_uint64), C.c_int32]
     lib.sfa_fwd_probe_read.restype = C.c_int
     lib.sfa_release_workspaces.restype = None
+    lib.sfa_decode_sharded.argtypes = [C.POINTER(DecodeArgs), C.POINTER(ShardComm), C.c_void_p]
+    lib.sfa_decode_sharded.restype = C.c_int
+    lib.sfa_shard_merge.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                    C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
+    lib.sfa_shard_merge.restype = C.c_int
+    lib.sfa_shard_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.sfa_shard_workspace_bytes.restype = C.c_size_t
+    lib.sfa_peer_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
+    lib.sfa_peer_alloc.restype = C.c_int
+    lib.sfa_peer_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.sfa_peer_open.restype = C.c_int
+    lib.sfa_peer_close.argtypes = [C.c_void_p]
+    lib.sfa_peer_close.restype = C.c_int
+    lib.sfa_peer_free.argtypes = [C.c_void_p]
+    lib.sfa_peer_free.restype = C.c_int
+    lib.sfa_shard_watchdog.argtypes = [C.c_int]
+    lib.sfa_shard_watchdog.restype = C.c_int
     return lib
 
 

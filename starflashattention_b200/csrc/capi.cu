@@ -5,6 +5,7 @@
 
 #include <math.h>
 #include <stdio.h>
+#include <string.h>
 
 #include <src/flash_attn.h>
 
@@ -142,6 +143,56 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     return decode_impl(d, /*seqlen_add=*/1, stream, &f);
 }
 
+// Local split-KV pass of the sharded decode: always leaves (o_part, ml_part) in the workspace.
+int decode_sharded_impl(const sfa_decode_args& a, const sfa_shard_comm& c, cudaStream_t stream) {
+    int rc = check_dtype(a.dtype);
+    if (rc) return rc;
+    if (!a.q || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "sharded decode: null tensor pointer");
+    if (c.world < 1 || c.world > 8 || c.rank < 0 || c.rank >= c.world)
+        return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8 and 0 <= rank < world");
+    if (c.mode != 0 && c.mode != 1) return fail(SFA_ERR_INVALID, "sharded decode: mode must be 0 (peer exchange) or 1 (publish)");
+    if (c.mode == 0)
+        for (int r = 0; r < c.world; ++r)
+            if (!c.peer_ws[r]) return fail(SFA_ERR_INVALID, "sharded decode: missing peer workspace pointer");
+    if (c.mode == 1 && !c.payload) return fail(SFA_ERR_INVALID, "sharded decode: publish mode needs a payload buffer");
+    if (a.heads_kv <= 0 || a.heads_q % a.heads_kv) return fail(SFA_ERR_INVALID, "sharded decode: heads_q must be a multiple of heads_kv");
+    if (a.batch <= 0) return SFA_OK;
+    const DeviceInfo* dev = current_device();
+    if (!dev) return SFA_ERR_NO_DEVICE;
+
+    DecodeLaunch L;
+    L.q = a.q; L.k = a.k_cache; L.v = a.v_cache; L.seqlens = a.seqlens; L.o = a.o; L.lse = a.lse;
+    L.batch = a.batch; L.seqlen_k = a.seqlen_k; L.heads_q = a.heads_q; L.heads_kv = a.heads_kv; L.head_dim = a.head_dim;
+    L.q_bs = a.q_batch_stride; L.q_hs = a.q_head_stride;
+    L.k_bs = a.k_batch_stride; L.k_rs = a.k_row_stride; L.k_hs = a.k_head_stride;
+    L.v_bs = a.v_batch_stride; L.v_rs = a.v_row_stride; L.v_hs = a.v_head_stride;
+    L.o_bs = a.o_batch_stride; L.o_hs = a.o_head_stride;
+    L.scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
+    L.seqlen_add = 0;
+    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv, a.seqlen_k, dev->sm_count);
+    L.dtype = a.dtype;
+    L.force_partials = true;
+    const size_t rows = (size_t)a.batch * a.heads_q * L.num_splits;
+    const size_t need = rows * a.head_dim * sizeof(float) + rows * sizeof(float2) + 256;
+    uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
+    if (ws) {
+        if (a.workspace_bytes < need) return fail(SFA_ERR_INVALID, "sharded decode: workspace too small, need " + std::to_string(need) + " bytes");
+    } else {
+        ws = reinterpret_cast<uint8_t*>(get_workspace(need, stream));
+        if (!ws) return SFA_ERR_CUDA;
+    }
+    L.o_part = reinterpret_cast<float*>(ws);
+    L.ml_part = reinterpret_cast<float2*>(ws + align_up(rows * a.head_dim * sizeof(float), 16));
+    if ((rc = launch_decode(L, stream))) return rc;
+
+    ShardLaunch S = {};
+    S.o_part = L.o_part; S.ml_part = L.ml_part; S.num_splits = L.num_splits;
+    S.o = a.o; S.lse = a.lse; S.o_bs = a.o_batch_stride; S.o_hs = a.o_head_stride;
+    S.batch = a.batch; S.heads_q = a.heads_q; S.head_dim = a.head_dim; S.dtype = a.dtype;
+    S.rank = c.rank; S.world = c.world; S.step = c.step; S.peer_ws = c.peer_ws; S.payload = c.payload; S.mode = c.mode;
+    return launch_shard_exchange(S, stream);
+}
+
 }  // namespace
 }  // namespace sfa
 
@@ -172,6 +223,69 @@ size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_d
 int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decoder_step: null args");
     return sfa::decoder_step_impl(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode_sharded(const sfa_decode_args* local_args, const sfa_shard_comm* comm, void* stream) {
+    if (!local_args || !comm) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_sharded: null args");
+    return sfa::decode_sharded_impl(*local_args, *comm, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_shard_merge(const float* payloads, int32_t world, void* o, float* lse, int32_t batch, int32_t heads_q,
+                    int32_t head_dim, int64_t o_batch_stride, int64_t o_head_stride, int32_t dtype, void* stream) {
+    int rc = sfa::check_dtype(dtype);
+    if (rc) return rc;
+    if (!payloads || !o) return sfa::fail(SFA_ERR_INVALID, "sfa_shard_merge: null pointer");
+    if (batch <= 0) return SFA_OK;
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    sfa::ShardLaunch S = {};
+    S.o = o; S.lse = lse; S.o_bs = o_batch_stride; S.o_hs = o_head_stride;
+    S.batch = batch; S.heads_q = heads_q; S.head_dim = head_dim; S.dtype = dtype;
+    S.rank = 0; S.world = world; S.payload = const_cast<float*>(payloads); S.mode = 2;
+    return sfa::launch_shard_exchange(S, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t sfa_shard_workspace_bytes(int32_t world, int32_t batch, int32_t heads_q, int32_t head_dim) {
+    return sfa::shard_workspace_bytes(world, batch * heads_q, head_dim);
+}
+
+int sfa_peer_alloc(size_t bytes, void** ptr, uint8_t handle[64]) {
+    if (!ptr || !handle || bytes == 0) return sfa::fail(SFA_ERR_INVALID, "sfa_peer_alloc: bad arguments");
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    SFA_CUDA_CHECK(cudaMalloc(ptr, bytes));
+    SFA_CUDA_CHECK(cudaMemset(*ptr, 0, bytes));
+    SFA_CUDA_CHECK(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    SFA_CUDA_CHECK(cudaIpcGetMemHandle(&h, *ptr));
+    memcpy(handle, &h, 64);
+    return SFA_OK;
+}
+
+int sfa_peer_open(const uint8_t handle[64], void** ptr) {
+    if (!ptr || !handle) return sfa::fail(SFA_ERR_INVALID, "sfa_peer_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    SFA_CUDA_CHECK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return SFA_OK;
+}
+
+int sfa_peer_close(void* ptr) {
+    if (ptr) SFA_CUDA_CHECK(cudaIpcCloseMemHandle(ptr));
+    return SFA_OK;
+}
+
+int sfa_peer_free(void* ptr) {
+    if (ptr) SFA_CUDA_CHECK(cudaFree(ptr));
+    return SFA_OK;
+}
+
+int sfa_shard_watchdog(int clear) {
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return sfa::fail(SFA_ERR_CUDA, std::string("cudaDeviceSynchronize: ") + cudaGetErrorString(e));
+    int v = 0;
+    int rc = sfa::shard_error_flag_read(&v, clear);
+    return rc ? rc : v;
 }
 
 int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int32_t rot_dim, int32_t dtype, void* stream) {

@@ -95,6 +95,7 @@ struct DecodeParams {
     const void* sin_table;
     int64_t qkv_stride;
     int rotary_dim, heads_kv;
+    int force_partials;
 };
 
 // Shared memory used only for the end-of-CTA merge of the four warp states.
@@ -294,7 +295,7 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
             acc += sc * sm.o[w][hh][d];
         }
         const int hq = hk * g + hh;
-        if (p.num_splits == 1) {
+        if (p.num_splits == 1 && !p.force_partials) {
             const float inv = L > 0.f ? 1.f / L : 0.f;
             T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
             orow[d] = (T)(acc * inv);
@@ -342,7 +343,7 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
     else decode_splitkv_kernel<T, D, false><<<grid, kWarps * 32, 0, stream>>>(p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
-    if (a.num_splits > 1) {
+    if (a.num_splits > 1 && !a.force_partials) {
         dim3 cgrid(a.heads_q, a.batch);
         decode_combine_kernel<T, D><<<cgrid, D, a.num_splits * sizeof(float), stream>>>(p);
         SFA_CUDA_CHECK(cudaGetLastError());
@@ -366,7 +367,7 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
     long s = (slots + units - 1) / units;
     const long max_by_len = max_seqlen / 256 > 0 ? max_seqlen / 256 : 1;
     if (s > max_by_len) s = max_by_len;
-    if (s > 128) s = 128;
+    if (s > 256) s = 256;   // one long sequence (batch 1): 8 kv-heads x 222 chunks fill 4 waves of 3 CTAs/SM
     if (s < 1) s = 1;
     return (int)s;
 }
@@ -392,7 +393,7 @@ int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     p.num_splits = a.num_splits;
     p.scale_log2 = a.scale * kLog2e;
     p.qkv = a.fused_qkv; p.cos_table = a.cos_table; p.sin_table = a.sin_table; p.qkv_stride = a.qkv_stride;
-    p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv;
+    p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv; p.force_partials = a.force_partials ? 1 : 0;
     if (a.dtype == SFA_FP16) {
         return a.head_dim == 128 ? launch_typed<__half, 128>(a, p, stream) : launch_typed<__half, 64>(a, p, stream);
     }

@@ -53,10 +53,26 @@ struct DecodeLaunch {
     const void* cos_table = nullptr; const void* sin_table = nullptr;
     int64_t qkv_stride = 0;
     int rotary_dim = 0;
+    bool force_partials = false;   // write (o_part, ml_part) even with one split (cross-GPU sharded decode)
 };
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count);
 size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits);
 int launch_decode(const DecodeLaunch& p, cudaStream_t stream);
+
+// ------------------------------------------------------------------ cross-GPU split-KV decode (shard_sm100.cu)
+struct ShardLaunch {
+    const float* o_part; const float2* ml_part; int num_splits;   // this rank's split partials (modes 0, 1)
+    void* o; float* lse; int64_t o_bs, o_hs;
+    int batch, heads_q, head_dim, dtype;
+    int rank, world;
+    uint32_t step;
+    void* const* peer_ws;   // mode 0: world pointers, peer_ws[rank] = own workspace
+    float* payload;         // mode 1: (rows, D + 1) out; mode 2: (world, rows, D + 1) in
+    int mode;               // 0 fused peer exchange + merge, 1 publish only, 2 merge gathered payloads
+};
+size_t shard_workspace_bytes(int world, int rows, int head_dim);
+int launch_shard_exchange(const ShardLaunch& a, cudaStream_t stream);
+int shard_error_flag_read(int* value, int clear);
 
 // ------------------------------------------------------------------ rope / cache (rope_cache.cu)
 struct RopeAppendLaunch {

@@ -4,6 +4,10 @@ Every (batch, kv-head group) of an attention call is independent (SURVEY.md sect
 path partitions with no exchange step: one process per GPU (torchrun), each rank runs the
 single-GPU kernels on its own contiguous slice of units, and nothing crosses NVLink inside the
 timed path.  ``gather_for_verification`` is the only collective and exists for tests.
+
+The one place with a real exchange step is a single long sequence whose KV length is cut over the GPUs
+(``KVShardedDecode``): each rank attends over its shard and the ranks swap
+(O, LSE) rows - 16.5 KB per rank at C4's head shape - through peer memory inside the merge kernel.
 """
 from __future__ import annotations
 
@@ -102,3 +106,133 @@ def gather_for_verification(local_full: torch.Tensor) -> torch.Tensor:
         dist.all_reduce(t)
         return t.to(local_full.dtype)
     return local_full
+
+
+# --------------------------------------------------------------------------- KV-length sharding (row f2)
+def kv_shard_range(total_len: int, world_size: int, rank: int, multiple: int = 64) -> range:
+    """Keys [begin, end) of a cache of ``total_len`` rows owned by ``rank``: equal shards rounded up to a
+    multiple of ``multiple`` rows (the last ranks may own fewer rows, or none)."""
+    if world_size <= 0 or not (0 <= rank < world_size):
+        raise ValueError("bad world_size / rank")
+    shard = -(-total_len // world_size)
+    shard = -(-shard // multiple) * multiple
+    begin = min(total_len, rank * shard)
+    return range(begin, min(total_len, begin + shard))
+
+
+def local_seqlens(seqlens: torch.Tensor, shard: range) -> torch.Tensor:
+    """Visible keys of every sequence inside ``shard`` (global lengths clipped to the shard)."""
+    return (seqlens.to(torch.int64) - shard.start).clamp_(0, len(shard)).to(torch.int32)
+
+
+class KVShardedDecode:
+    """Split-KV decode of sequences whose KV length is sharded over ``world`` GPUs, one process per GPU.
+
+    ``exchange="peer"``: the merge kernel stores this rank's (O, LSE) rows into every peer's workspace over
+    NVLink and merges the world's rows in the same launch (CUDA-IPC mapped buffers; ``torch.distributed`` is
+    used once, to hand the 64-byte IPC handles around).  ``exchange="nccl"``: publish kernel, NCCL
+    ``all_gather_into_tensor``, merge kernel - the baseline the fused form is measured against.
+    ``peer_ws`` lets a test emulate several ranks inside one process by passing the workspaces directly."""
+
+    def __init__(self, batch: int, heads_q: int, heads_kv: int, head_dim: int, shard_len: int, rank: int, world: int,
+                 device, exchange: str = "peer", group=None, peer_ws: Optional[List[int]] = None):
+        from . import _capi
+        if exchange not in ("peer", "nccl"):
+            raise ValueError("exchange must be 'peer' or 'nccl'")
+        self._capi, self.lib = _capi, _capi.lib
+        self.batch, self.heads_q, self.heads_kv, self.head_dim = batch, heads_q, heads_kv, head_dim
+        self.rank, self.world, self.exchange, self.group = rank, world, exchange, group
+        self.device = torch.device(device)
+        self.step = 0
+        self._owned = None
+        self._opened: List[int] = []
+        rows = batch * heads_q
+        with torch.cuda.device(self.device):
+            a = _capi.DecodeArgs()
+            a.batch, a.seqlen_k, a.heads_kv, a.num_splits = batch, max(1, shard_len), heads_kv, 0
+            self.num_splits = max(1, int(self.lib.sfa_decode_num_splits(a)))
+            part = rows * self.num_splits
+            self.workspace = torch.empty(part * head_dim * 4 + part * 8 + 512, dtype=torch.uint8, device=self.device)
+            if exchange == "nccl":
+                self.payload = torch.empty((rows * (head_dim + 1),), dtype=torch.float32, device=self.device)
+                self.gathered = torch.empty((world, rows * (head_dim + 1)), dtype=torch.float32, device=self.device)
+                self.peers = None
+            elif peer_ws is not None:
+                self.peers = list(peer_ws)
+            else:
+                import ctypes as C
+                import torch.distributed as dist
+                nbytes = int(self.lib.sfa_shard_workspace_bytes(world, batch, heads_q, head_dim))
+                ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+                _capi.check(self.lib.sfa_peer_alloc(nbytes, C.byref(ptr), handle))
+                self._owned = ptr.value
+                handles: List[Optional[bytes]] = [handle.raw] * world
+                if world > 1:
+                    dist.all_gather_object(handles, handle.raw, group=group)
+                self.peers = []
+                for r in range(world):
+                    if r == rank:
+                        self.peers.append(self._owned)
+                    else:
+                        p = C.c_void_p()
+                        _capi.check(self.lib.sfa_peer_open(handles[r], C.byref(p)))
+                        self._opened.append(p.value)
+                        self.peers.append(p.value)
+                if world > 1:
+                    dist.barrier(group=group)
+
+    @staticmethod
+    def workspace_bytes(world: int, batch: int, heads_q: int, head_dim: int) -> int:
+        from . import _capi
+        return int(_capi.lib.sfa_shard_workspace_bytes(world, batch, heads_q, head_dim))
+
+    def decode(self, q: torch.Tensor, k_shard: torch.Tensor, v_shard: torch.Tensor, seqlens_local: torch.Tensor,
+               out: Optional[torch.Tensor] = None, lse: Optional[torch.Tensor] = None,
+               softmax_scale: Optional[float] = None):
+        """q (B, Hq, D); k_shard / v_shard (B, shard_len, Hkv, D): this rank's rows of the cache; seqlens_local
+        int32 (B): visible keys inside the shard.  Returns the full (out, lse) on every rank, asynchronously on
+        the current stream."""
+        from .interface import _decode_args, _stream
+        capi = self._capi
+        if out is None:
+            out = torch.empty_like(q)
+        if lse is None:
+            lse = torch.empty(q.shape[:2], dtype=torch.float32, device=q.device)
+        a = _decode_args(q, k_shard, v_shard, seqlens_local, out, lse, softmax_scale, self.num_splits)
+        a.workspace, a.workspace_bytes = self.workspace.data_ptr(), self.workspace.numel()
+        self.step += 1
+        c = capi.ShardComm()
+        c.rank, c.world, c.step = self.rank, self.world, self.step
+        with torch.cuda.device(self.device):
+            if self.exchange == "peer":
+                c.mode = 0
+                for r in range(self.world):
+                    c.peer_ws[r] = self.peers[r]
+                capi.check(self.lib.sfa_decode_sharded(a, c, _stream()))
+            else:
+                import torch.distributed as dist
+                c.mode, c.payload = 1, self.payload.data_ptr()
+                capi.check(self.lib.sfa_decode_sharded(a, c, _stream()))
+                dist.all_gather_into_tensor(self.gathered, self.payload, group=self.group)
+                capi.check(self.lib.sfa_shard_merge(self.gathered.data_ptr(), self.world, out.data_ptr(), lse.data_ptr(),
+                                                    q.shape[0], q.shape[1], q.shape[2], out.stride(0), out.stride(1),
+                                                    a.dtype, _stream()))
+        return out, lse
+
+    def watchdog(self, clear: bool = True) -> int:
+        return int(self.lib.sfa_shard_watchdog(1 if clear else 0))
+
+    def close(self):
+        """Unmaps the peers' buffers and frees the own one (collective: every rank calls it)."""
+        if self._owned is None:
+            return
+        torch.cuda.synchronize(self.device)
+        for p in self._opened:
+            self.lib.sfa_peer_close(p)
+        self._opened = []
+        if self.world > 1:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.barrier(group=self.group)
+        self.lib.sfa_peer_free(self._owned)
+        self._owned = None
