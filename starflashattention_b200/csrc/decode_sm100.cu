@@ -20,6 +20,7 @@
 // each thread's K fragment is one contiguous 16-byte load, and the output head_dim axis of P.V is
 // permuted such that each thread's V fragment comes from 16-byte loads too (two PRMTs per MMA).
 #include "internal.h"
+#include "merge.cuh"
 #include "rope.cuh"
 
 #include <math.h>
@@ -310,30 +311,19 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
 
 // Merge of the per-split partials (reference flash_combine_kernel, src/flash_attn.cu:877-935, in fp32).
 template <typename T, int D>
-__global__ void __launch_bounds__(D) decode_combine_kernel(const DecodeParams p) {
+__global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const DecodeParams p) {
     extern __shared__ float w_sm[];   // num_splits weights
-    __shared__ float red[2];
+    __shared__ MergeScratch<D> sc;
     const int hq = blockIdx.x, b = blockIdx.y;
     const int64_t row0 = ((int64_t)b * p.heads_q + hq) * p.num_splits;
-    const int S = p.num_splits;
-    // Every thread scans the (m, l) pairs; S is a few dozen at most.
-    float M = -INFINITY;
-    for (int s = 0; s < S; ++s) M = fmaxf(M, p.ml_part[row0 + s].x);
-    float L = 0.f;
-    for (int s = threadIdx.x; s < S; s += D) {
-        const float2 ml = p.ml_part[row0 + s];
-        w_sm[s] = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - M);
+    float acc, L, M;
+    merge_splits<D>(p.o_part, p.ml_part, row0, p.num_splits, w_sm, sc, acc, L, M);
+    if (threadIdx.x < D) {
+        const float inv = L > 0.f ? 1.f / L : 0.f;
+        T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
+        orow[threadIdx.x] = (T)(acc * inv);
+        if (threadIdx.x == 0 && p.lse) p.lse[(int64_t)b * p.heads_q + hq] = L > 0.f ? (M + log2f(L)) * kLn2 : -INFINITY;
     }
-    __syncthreads();
-    for (int s = 0; s < S; ++s) L += w_sm[s] * p.ml_part[row0 + s].y;
-    float acc = 0.f;
-    const float* op = p.o_part + row0 * D + threadIdx.x;
-    for (int s = 0; s < S; ++s) acc += w_sm[s] * op[(int64_t)s * D];
-    const float inv = L > 0.f ? 1.f / L : 0.f;
-    T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
-    orow[threadIdx.x] = (T)(acc * inv);
-    if (threadIdx.x == 0 && p.lse) p.lse[(int64_t)b * p.heads_q + hq] = L > 0.f ? (M + log2f(L)) * kLn2 : -INFINITY;
-    (void)red;
 }
 
 template <typename T, int D>
@@ -345,7 +335,7 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
     count_launch();
     if (a.num_splits > 1 && !a.force_partials) {
         dim3 cgrid(a.heads_q, a.batch);
-        decode_combine_kernel<T, D><<<cgrid, D, a.num_splits * sizeof(float), stream>>>(p);
+        decode_combine_kernel<T, D><<<cgrid, D * kMergeGroups, a.num_splits * sizeof(float), stream>>>(p);
         SFA_CUDA_CHECK(cudaGetLastError());
         count_launch();
     }

@@ -1,0 +1,75 @@
+// Merge of split-KV partials by one thread block (the reference's flash_combine_kernel,
+// src/flash_attn.cu:877-935, in fp32 and with the split axis spread over the block so that a row with a few
+// hundred splits is not a serial chain of loads).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+namespace sfa {
+
+constexpr int kMergeGroups = 4;   // blockDim.x = D * kMergeGroups; thread = (group g, head_dim element d)
+
+template <int D>
+struct MergeScratch {
+    float red[32];                       // cross-warp reductions
+    float acc[kMergeGroups][D];
+};
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// o_part (rows, S, D) un-normalised partial outputs, ml_part (rows, S) = (m in log2 units, l).  On return every
+// thread holds M and L of the row; threads of group 0 hold acc = sum_s 2^(m_s - M) o_s[d].  w_sm: S floats.
+template <int D>
+__device__ __forceinline__ void merge_splits(const float* __restrict__ o_part, const float2* __restrict__ ml_part,
+                                             int64_t row0, int S, float* w_sm, MergeScratch<D>& sc, float& acc,
+                                             float& L, float& M) {
+    constexpr int T = D * kMergeGroups, W = T / 32;
+    const int tid = threadIdx.x, g = tid / D, d = tid - g * D, warp = tid >> 5, lane = tid & 31;
+    float m = -INFINITY;
+    for (int s = tid; s < S; s += T) m = fmaxf(m, ml_part[row0 + s].x);
+    m = warp_max(m);
+    if (lane == 0) sc.red[warp] = m;
+    __syncthreads();
+    m = lane < W ? sc.red[lane] : -INFINITY;
+    M = warp_max(m);
+    __syncthreads();
+    float l = 0.f;
+    for (int s = tid; s < S; s += T) {
+        const float2 ml = ml_part[row0 + s];
+        const float w = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - M);
+        w_sm[s] = w;
+        l += w * ml.y;
+    }
+    l = warp_sum(l);
+    if (lane == 0) sc.red[warp] = l;
+    __syncthreads();                      // also publishes w_sm
+    l = lane < W ? sc.red[lane] : 0.f;
+    L = warp_sum(l);
+    float a0 = 0.f, a1 = 0.f;
+    const float* op = o_part + row0 * D + d;
+    int s = g;
+    for (; s + kMergeGroups < S; s += 2 * kMergeGroups) {
+        a0 += w_sm[s] * op[(int64_t)s * D];
+        a1 += w_sm[s + kMergeGroups] * op[(int64_t)(s + kMergeGroups) * D];
+    }
+    if (s < S) a0 += w_sm[s] * op[(int64_t)s * D];
+    sc.acc[g][d] = a0 + a1;
+    __syncthreads();
+    acc = 0.f;
+    if (g == 0) {
+#pragma unroll
+        for (int i = 0; i < kMergeGroups; ++i) acc += sc.acc[i][d];
+    }
+}
+
+}  // namespace sfa

@@ -11,6 +11,7 @@
 // step ahead of a peer (it needs the peer's flags of step s+1 to finish step s+1), so slot (s & 1) is quiescent
 // when step s+2 writes it.  Flags hold the step number and are never reset.
 #include "internal.h"
+#include "merge.cuh"
 
 #include <math.h>
 
@@ -64,33 +65,24 @@ __device__ int g_shard_error;
 // MODE 0: fused exchange + merge over peer memory.  MODE 1: publish this rank's (O, LSE) to p.payload only.
 // MODE 2: merge `world` gathered payloads laid out (world, rows, D + 1) at p.payload (after an all-gather).
 template <typename T, int D, int MODE>
-__global__ void __launch_bounds__(D) shard_exchange_kernel(const ShardParams p) {
+__global__ void __launch_bounds__(D * kMergeGroups) shard_exchange_kernel(const ShardParams p) {
     extern __shared__ float w_sm[];   // num_splits weights
+    __shared__ MergeScratch<D> sc;
     __shared__ float lse_sm[kMaxWorld];
     __shared__ int ok_sm;
     const int hq = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int row = b * p.heads_q + hq;
     float o_n = 0.f, lse2 = -INFINITY;
     if constexpr (MODE != 2) {
-        // ---- (1) merge this rank's splits
-        const int64_t row0 = (int64_t)row * p.num_splits;
-        const int S = p.num_splits;
-        float M = -INFINITY;
-        for (int s = 0; s < S; ++s) M = fmaxf(M, p.ml_part[row0 + s].x);
-        for (int s = tid; s < S; s += D) {
-            const float2 ml = p.ml_part[row0 + s];
-            w_sm[s] = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - M);
-        }
-        __syncthreads();
-        float L = 0.f, acc = 0.f;
-        for (int s = 0; s < S; ++s) L += w_sm[s] * p.ml_part[row0 + s].y;
-        const float* op = p.o_part + row0 * D + tid;
-        for (int s = 0; s < S; ++s) acc += w_sm[s] * op[(int64_t)s * D];
+        // ---- (1) merge this rank's splits (whole block); the rest of the kernel is the first D threads' work
+        float acc, L, M;
+        merge_splits<D>(p.o_part, p.ml_part, (int64_t)row * p.num_splits, p.num_splits, w_sm, sc, acc, L, M);
         o_n = L > 0.f ? acc / L : 0.f;
         lse2 = L > 0.f ? M + log2f(L) : -INFINITY;
     }
+    const bool worker = tid < D;
     if constexpr (MODE == 1) {
-        p.payload[(size_t)row * D + tid] = o_n;
+        if (worker) p.payload[(size_t)row * D + tid] = o_n;
         if (tid == 0) p.payload[(size_t)p.rows * D + row] = lse2;
         return;
     }
@@ -101,7 +93,7 @@ __global__ void __launch_bounds__(D) shard_exchange_kernel(const ShardParams p) 
 #pragma unroll 1
         for (int dst = 0; dst < p.world; ++dst) {
             float* slot = reinterpret_cast<float*>(p.ws[dst] + slot_offset(parity, p.rank, p.world, p.rows, D));
-            slot[(size_t)row * D + tid] = o_n;
+            if (worker) slot[(size_t)row * D + tid] = o_n;
             if (tid == 0) slot[(size_t)p.rows * D + row] = lse2;
         }
         __threadfence_system();
@@ -147,11 +139,11 @@ __global__ void __launch_bounds__(D) shard_exchange_kernel(const ShardParams p) 
         if (r < p.world) {
             const float w = lse_sm[r] == -INFINITY ? 0.f : exp2f(lse_sm[r] - M);
             W += w;
-            acc += w * __ldcg(src_base[r] + (size_t)row * D + tid);
+            if (worker) acc += w * __ldcg(src_base[r] + (size_t)row * D + tid);
         }
     }
     T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
-    orow[tid] = (T)(W > 0.f ? acc / W : 0.f);
+    if (worker) orow[tid] = (T)(W > 0.f ? acc / W : 0.f);
     if (tid == 0 && p.lse) p.lse[row] = W > 0.f ? (M + log2f(W)) * kLn2 : -INFINITY;
 }
 
@@ -159,9 +151,9 @@ template <typename T, int D>
 int launch_mode(const ShardParams& p, int mode, int batch, cudaStream_t stream) {
     dim3 grid(p.heads_q, batch);
     const size_t smem = (size_t)(p.num_splits > 0 ? p.num_splits : 1) * sizeof(float);
-    if (mode == 0) shard_exchange_kernel<T, D, 0><<<grid, D, smem, stream>>>(p);
-    else if (mode == 1) shard_exchange_kernel<T, D, 1><<<grid, D, smem, stream>>>(p);
-    else shard_exchange_kernel<T, D, 2><<<grid, D, smem, stream>>>(p);
+    if (mode == 0) shard_exchange_kernel<T, D, 0><<<grid, D * kMergeGroups, smem, stream>>>(p);
+    else if (mode == 1) shard_exchange_kernel<T, D, 1><<<grid, D * kMergeGroups, smem, stream>>>(p);
+    else shard_exchange_kernel<T, D, 2><<<grid, D * kMergeGroups, smem, stream>>>(p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return SFA_OK;
