@@ -121,6 +121,12 @@ typedef struct sfa_shard_comm {
 } sfa_shard_comm;
 
 int sfa_decode_sharded(const sfa_decode_args* local_args, const sfa_shard_comm* comm, void* stream);
+/* Test aid: `world` ranks emulated on ONE GPU.  args[r] is rank r's call (each with its own split workspace in
+ * args[r].workspace), ws[r] its exchange workspace (plain device memory of sfa_shard_workspace_bytes).  The
+ * local passes run back to back; the exchange blocks of all ranks go out as one cooperative launch, because
+ * separate launches that spin on each other's flags are not guaranteed to run at the same time on one GPU.
+ * Synchronises the stream. */
+int sfa_decode_sharded_emulated(const sfa_decode_args* args, int32_t world, void* const* ws, uint32_t step, void* stream);
 /* Merges `world` gathered payloads laid out (world, rows, head_dim + 1) into o / lse. */
 int sfa_shard_merge(const float* payloads, int32_t world, void* o, float* lse, int32_t batch, int32_t heads_q,
                     int32_t head_dim, int64_t o_batch_stride, int64_t o_head_stride, int32_t dtype, void* stream);

@@ -19,7 +19,7 @@ EXPORTED_SYMBOLS = (
     "sfa_fwd", "sfa_decode", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
-    "sfa_decode_sharded", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
+    "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
     "sfa_peer_close", "sfa_peer_free", "sfa_shard_watchdog",
 )
 # C++-mangled drop-ins of the reference's src/flash_attn.h:7-11.
@@ -113,6 +113,8 @@ def _load() -> C.CDLL:
     lib.sfa_release_workspaces.restype = None
     lib.sfa_decode_sharded.argtypes = [C.POINTER(DecodeArgs), C.POINTER(ShardComm), C.c_void_p]
     lib.sfa_decode_sharded.restype = C.c_int
+    lib.sfa_decode_sharded_emulated.argtypes = [C.POINTER(DecodeArgs), C.c_int32, C.POINTER(C.c_void_p), C.c_uint32, C.c_void_p]
+    lib.sfa_decode_sharded_emulated.restype = C.c_int
     lib.sfa_shard_merge.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     lib.sfa_shard_merge.restype = C.c_int

@@ -143,20 +143,16 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     return decode_impl(d, /*seqlen_add=*/1, stream, &f);
 }
 
-// Local split-KV pass of the sharded decode: always leaves (o_part, ml_part) in the workspace.
-int decode_sharded_impl(const sfa_decode_args& a, const sfa_shard_comm& c, cudaStream_t stream) {
+// Local split-KV pass of the sharded decode: always leaves (o_part, ml_part) in the workspace; fills the
+// exchange launch for this rank.
+int shard_local_pass(const sfa_decode_args& a, int rank, int world, ShardLaunch& S, cudaStream_t stream) {
     int rc = check_dtype(a.dtype);
     if (rc) return rc;
     if (!a.q || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "sharded decode: null tensor pointer");
-    if (c.world < 1 || c.world > 8 || c.rank < 0 || c.rank >= c.world)
+    if (world < 1 || world > 8 || rank < 0 || rank >= world)
         return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8 and 0 <= rank < world");
-    if (c.mode != 0 && c.mode != 1) return fail(SFA_ERR_INVALID, "sharded decode: mode must be 0 (peer exchange) or 1 (publish)");
-    if (c.mode == 0)
-        for (int r = 0; r < c.world; ++r)
-            if (!c.peer_ws[r]) return fail(SFA_ERR_INVALID, "sharded decode: missing peer workspace pointer");
-    if (c.mode == 1 && !c.payload) return fail(SFA_ERR_INVALID, "sharded decode: publish mode needs a payload buffer");
     if (a.heads_kv <= 0 || a.heads_q % a.heads_kv) return fail(SFA_ERR_INVALID, "sharded decode: heads_q must be a multiple of heads_kv");
-    if (a.batch <= 0) return SFA_OK;
+    if (a.batch <= 0) return fail(SFA_ERR_INVALID, "sharded decode: batch must be positive");
     const DeviceInfo* dev = current_device();
     if (!dev) return SFA_ERR_NO_DEVICE;
 
@@ -185,12 +181,42 @@ int decode_sharded_impl(const sfa_decode_args& a, const sfa_shard_comm& c, cudaS
     L.ml_part = reinterpret_cast<float2*>(ws + align_up(rows * a.head_dim * sizeof(float), 16));
     if ((rc = launch_decode(L, stream))) return rc;
 
-    ShardLaunch S = {};
+    S = ShardLaunch{};
     S.o_part = L.o_part; S.ml_part = L.ml_part; S.num_splits = L.num_splits;
     S.o = a.o; S.lse = a.lse; S.o_bs = a.o_batch_stride; S.o_hs = a.o_head_stride;
     S.batch = a.batch; S.heads_q = a.heads_q; S.head_dim = a.head_dim; S.dtype = a.dtype;
-    S.rank = c.rank; S.world = c.world; S.step = c.step; S.peer_ws = c.peer_ws; S.payload = c.payload; S.mode = c.mode;
+    S.rank = rank; S.world = world;
+    return SFA_OK;
+}
+
+int decode_sharded_impl(const sfa_decode_args& a, const sfa_shard_comm& c, cudaStream_t stream) {
+    if (c.mode != 0 && c.mode != 1) return fail(SFA_ERR_INVALID, "sharded decode: mode must be 0 (peer exchange) or 1 (publish)");
+    if (c.world < 1 || c.world > 8 || c.rank < 0 || c.rank >= c.world)
+        return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8 and 0 <= rank < world");
+    if (c.mode == 0)
+        for (int r = 0; r < c.world; ++r)
+            if (!c.peer_ws[r]) return fail(SFA_ERR_INVALID, "sharded decode: missing peer workspace pointer");
+    if (c.mode == 1 && !c.payload) return fail(SFA_ERR_INVALID, "sharded decode: publish mode needs a payload buffer");
+    ShardLaunch S;
+    int rc = shard_local_pass(a, c.rank, c.world, S, stream);
+    if (rc) return rc;
+    S.step = c.step; S.peer_ws = c.peer_ws; S.payload = c.payload; S.mode = c.mode;
     return launch_shard_exchange(S, stream);
+}
+
+// Test aid: `world` ranks on ONE GPU.  The local passes run one after the other; the exchange of all ranks is one
+// cooperative launch.  Every rank's args must carry its own split workspace.
+int decode_sharded_emulated_impl(const sfa_decode_args* args, int world, void* const* ws, uint32_t step, cudaStream_t stream) {
+    if (world < 1 || world > 8) return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8");
+    ShardLaunch S[8];
+    for (int r = 0; r < world; ++r) {
+        if (!args[r].workspace) return fail(SFA_ERR_INVALID, "emulated sharded decode: every rank needs its own workspace");
+        if (!ws[r]) return fail(SFA_ERR_INVALID, "emulated sharded decode: missing exchange workspace");
+        int rc = shard_local_pass(args[r], r, world, S[r], stream);
+        if (rc) return rc;
+        S[r].step = step; S[r].peer_ws = ws; S[r].mode = 0;
+    }
+    return launch_shard_exchange_emulated(S, world, stream);
 }
 
 }  // namespace
@@ -228,6 +254,11 @@ int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream) {
 int sfa_decode_sharded(const sfa_decode_args* local_args, const sfa_shard_comm* comm, void* stream) {
     if (!local_args || !comm) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_sharded: null args");
     return sfa::decode_sharded_impl(*local_args, *comm, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode_sharded_emulated(const sfa_decode_args* args, int32_t world, void* const* ws, uint32_t step, void* stream) {
+    if (!args || !ws) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_sharded_emulated: null args");
+    return sfa::decode_sharded_emulated_impl(args, world, ws, step, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sfa_shard_merge(const float* payloads, int32_t world, void* o, float* lse, int32_t batch, int32_t heads_q,

@@ -72,6 +72,8 @@ struct ShardLaunch {
 };
 size_t shard_workspace_bytes(int world, int rows, int head_dim);
 int launch_shard_exchange(const ShardLaunch& a, cudaStream_t stream);
+// All ranks' exchange blocks in one cooperative launch on one GPU (tests; synchronises the stream).
+int launch_shard_exchange_emulated(const ShardLaunch* ranks, int world, cudaStream_t stream);
 int shard_error_flag_read(int* value, int clear);
 
 // ------------------------------------------------------------------ rope / cache (rope_cache.cu)

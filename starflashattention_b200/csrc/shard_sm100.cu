@@ -65,7 +65,7 @@ __device__ int g_shard_error;
 // MODE 0: fused exchange + merge over peer memory.  MODE 1: publish this rank's (O, LSE) to p.payload only.
 // MODE 2: merge `world` gathered payloads laid out (world, rows, D + 1) at p.payload (after an all-gather).
 template <typename T, int D, int MODE>
-__global__ void __launch_bounds__(D * kMergeGroups) shard_exchange_kernel(const ShardParams p) {
+__device__ __forceinline__ void shard_exchange_body(const ShardParams& p) {
     extern __shared__ float w_sm[];   // num_splits weights
     __shared__ MergeScratch<D> sc;
     __shared__ float lse_sm[kMaxWorld];
@@ -147,6 +147,30 @@ __global__ void __launch_bounds__(D * kMergeGroups) shard_exchange_kernel(const 
     if (tid == 0 && p.lse) p.lse[row] = W > 0.f ? (M + log2f(W)) * kLn2 : -INFINITY;
 }
 
+template <typename T, int D, int MODE>
+__global__ void __launch_bounds__(D * kMergeGroups) shard_exchange_kernel(const __grid_constant__ ShardParams p) {
+    shard_exchange_body<T, D, MODE>(p);
+}
+
+// Single-GPU emulation for tests: the blocks of ALL ranks in one cooperative launch (blockIdx.z = rank), so that the
+// blocks that spin on each other's flags are guaranteed to be co-resident.  (Separate launches that wait on one
+// another on one GPU have no such guarantee and have raised Xid 109 on this driver.)
+template <typename T, int D>
+__global__ void __launch_bounds__(D * kMergeGroups) shard_exchange_emulated_kernel(const ShardParams* per_rank) {
+    shard_exchange_body<T, D, 0>(per_rank[blockIdx.z]);
+}
+
+template <typename T, int D>
+int launch_emulated(const ShardParams* dev_params, int world, int heads_q, int batch, int num_splits_max, cudaStream_t stream) {
+    dim3 grid(heads_q, batch, world);
+    dim3 block(D * kMergeGroups);
+    size_t smem = (size_t)num_splits_max * sizeof(float);
+    void* kargs[] = {(void*)&dev_params};
+    SFA_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)shard_exchange_emulated_kernel<T, D>, grid, block, kargs, smem, stream));
+    count_launch();
+    return SFA_OK;
+}
+
 template <typename T, int D>
 int launch_mode(const ShardParams& p, int mode, int batch, cudaStream_t stream) {
     dim3 grid(p.heads_q, batch);
@@ -165,11 +189,12 @@ size_t shard_workspace_bytes(int world, int rows, int head_dim) {
     return flags_offset(world, rows, head_dim) + 2 * (size_t)world * rows * sizeof(uint32_t);
 }
 
-int launch_shard_exchange(const ShardLaunch& a, cudaStream_t stream) {
+namespace {
+int fill_params(const ShardLaunch& a, ShardParams& p) {
     if (a.world < 1 || a.world > kMaxWorld || a.rank < 0 || a.rank >= a.world)
         return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8 and 0 <= rank < world");
     if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
-    ShardParams p = {};
+    p = ShardParams{};
     p.o_part = a.o_part; p.ml_part = a.ml_part; p.num_splits = a.num_splits;
     p.o = a.o; p.lse = a.lse; p.o_bs = a.o_bs; p.o_hs = a.o_hs;
     p.heads_q = a.heads_q; p.rows = a.batch * a.heads_q;
@@ -179,10 +204,46 @@ int launch_shard_exchange(const ShardLaunch& a, cudaStream_t stream) {
     void* flag_addr = nullptr;
     SFA_CUDA_CHECK(cudaGetSymbolAddress(&flag_addr, g_shard_error));
     p.error_flag = reinterpret_cast<int*>(flag_addr);
+    return SFA_OK;
+}
+}  // namespace
+
+int launch_shard_exchange(const ShardLaunch& a, cudaStream_t stream) {
+    ShardParams p;
+    int rc = fill_params(a, p);
+    if (rc) return rc;
     if (a.dtype == SFA_FP16)
         return a.head_dim == 128 ? launch_mode<__half, 128>(p, a.mode, a.batch, stream) : launch_mode<__half, 64>(p, a.mode, a.batch, stream);
     return a.head_dim == 128 ? launch_mode<__nv_bfloat16, 128>(p, a.mode, a.batch, stream)
                              : launch_mode<__nv_bfloat16, 64>(p, a.mode, a.batch, stream);
+}
+
+int launch_shard_exchange_emulated(const ShardLaunch* ranks, int world, cudaStream_t stream) {
+    if (world < 1 || world > kMaxWorld) return fail(SFA_ERR_INVALID, "sharded decode: world must be 1..8");
+    ShardParams host[kMaxWorld];
+    int splits_max = 1;
+    for (int r = 0; r < world; ++r) {
+        int rc = fill_params(ranks[r], host[r]);
+        if (rc) return rc;
+        if (ranks[r].num_splits > splits_max) splits_max = ranks[r].num_splits;
+    }
+    ShardParams* dev = nullptr;
+    SFA_CUDA_CHECK(cudaMalloc(&dev, sizeof(ShardParams) * world));
+    cudaError_t e = cudaMemcpyAsync(dev, host, sizeof(ShardParams) * world, cudaMemcpyHostToDevice, stream);
+    int rc = SFA_OK;
+    if (e != cudaSuccess) rc = fail(SFA_ERR_CUDA, cudaGetErrorString(e));
+    const ShardLaunch& a = ranks[0];
+    if (!rc) {
+        if (a.dtype == SFA_FP16)
+            rc = a.head_dim == 128 ? launch_emulated<__half, 128>(dev, world, a.heads_q, a.batch, splits_max, stream)
+                                   : launch_emulated<__half, 64>(dev, world, a.heads_q, a.batch, splits_max, stream);
+        else
+            rc = a.head_dim == 128 ? launch_emulated<__nv_bfloat16, 128>(dev, world, a.heads_q, a.batch, splits_max, stream)
+                                   : launch_emulated<__nv_bfloat16, 64>(dev, world, a.heads_q, a.batch, splits_max, stream);
+    }
+    cudaStreamSynchronize(stream);     // test-only path: the parameter block is freed right away
+    cudaFree(dev);
+    return rc;
 }
 
 int shard_error_flag_read(int* value, int clear) {

@@ -1,7 +1,9 @@
-"""GPU parity of the cross-GPU split-KV decode on ONE device: the ranks of a box are
-emulated by streams of one process whose workspaces stand in for the peers' CUDA-IPC mappings, so the exchange
-kernel's stores, flags, waits and merge run exactly as they do over NVLink.  The real multi-process run is
-tools/shard_decode_bench.py under torchrun (profiles/r1c_shard_decode_n*.json)."""
+"""GPU parity of the cross-GPU split-KV decode on ONE device.  The ranks of a box
+are emulated through sfa_decode_sharded_emulated: each rank's split-KV pass runs on its shard, then the exchange
+blocks of ALL ranks go out as one cooperative launch whose workspaces stand in for the peers' CUDA-IPC mappings,
+so the stores, flags, waits and merge run as they do over NVLink.  (Ranks as separate launches that spin on each
+other on one GPU are not guaranteed to be co-resident - B200_PROFILING.md - so that form is not used.)  The real
+multi-process run is tools/shard_decode_bench.py under torchrun (profiles/r1c_shard*_n*.json)."""
 import pytest
 import torch
 
@@ -34,25 +36,29 @@ def test_peer_exchange_matches_oracle(dtype, world, B, Hq, Hkv, D, M, lens):
     vc = _rand((B, M, Hkv, D), dtype, 3)
     seqlens = torch.tensor(lens, dtype=torch.int32)
     o_ref, lse_ref = naive.decode_attention(q, kc, vc, seqlens)
+    import ctypes as C
+    from starflashattention_b200 import _capi
+    from starflashattention_b200.interface import _decode_args, _stream
     dev = torch.device("cuda:0")
     nbytes = multi_gpu.KVShardedDecode.workspace_bytes(world, B, Hq, D)
     ws = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
-    ptrs = [w.data_ptr() for w in ws]
+    ws_ptrs = (C.c_void_p * world)(*[w.data_ptr() for w in ws])
     qd, kd, vd = q.to(dev), kc.to(dev), vc.to(dev)
-    ranks, streams = [], [torch.cuda.Stream(device=dev) for _ in range(world)]
-    for r in range(world):
-        shard = multi_gpu.kv_shard_range(M, world, r)
-        ranks.append((shard, multi_gpu.KVShardedDecode(B, Hq, Hkv, D, len(shard), r, world, dev, peer_ws=ptrs)))
-    torch.cuda.synchronize()
-    for step in range(3):                                   # three steps: both parities of the double buffer, reuse
-        outs = []
-        for r, (shard, dec) in enumerate(ranks):
-            with torch.cuda.stream(streams[r]):
-                loc = multi_gpu.local_seqlens(seqlens, shard).to(dev)
-                o, lse = dec.decode(qd, kd[:, shard.start:shard.stop], vd[:, shard.start:shard.stop], loc)
-                outs.append((o, lse))
+    shards = [multi_gpu.kv_shard_range(M, world, r) for r in range(world)]
+    locs = [multi_gpu.local_seqlens(seqlens, sh).to(dev) for sh in shards]
+    splits = 5
+    part = [torch.empty(B * Hq * splits * (D * 4 + 8) + 512, dtype=torch.uint8, device=dev) for _ in range(world)]
+    for step in range(1, 4):                                # three steps: both parities of the double buffer, reuse
+        outs = [(torch.empty_like(qd), torch.empty((B, Hq), dtype=torch.float32, device=dev)) for _ in range(world)]
+        args = (_capi.DecodeArgs * world)()
+        for r, sh in enumerate(shards):
+            a = _decode_args(qd, kd[:, sh.start:sh.stop], vd[:, sh.start:sh.stop], locs[r], outs[r][0], outs[r][1],
+                             None, splits)
+            a.workspace, a.workspace_bytes = part[r].data_ptr(), part[r].numel()
+            args[r] = a
+        _capi.check(_capi.lib.sfa_decode_sharded_emulated(args, world, ws_ptrs, step, _stream()))
         torch.cuda.synchronize()
-        assert ranks[0][1].watchdog() == 0, "a rank waited more than 2 s for a peer's rows"
+        assert _capi.lib.sfa_shard_watchdog(1) == 0, "a rank waited more than 2 s for a peer's rows"
         for o, lse in outs:                                 # every rank holds the full result
             err = (o.float().cpu() - o_ref).abs()
             assert bool((err <= _bound(o_ref, dtype)).all()), float(err.max())
