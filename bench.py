@@ -52,6 +52,21 @@ def workload_units(name):
     return {"kind": kind, "amount": kv_bytes / 1e9, "unit": "GB/s", "metric": "decode_kv_gbs", "bound": "hbm"}
 
 
+def algorithmic_bytes(name):
+    kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
+    if kind == "fwd":
+        return 2.0 * B * S * D * (2 * Hq + 2 * Hkv) + 4.0 * B * Hq * S      # Q, O, K, V once + fp32 LSE
+    return 2.0 * B * S * Hkv * D * 2                                          # K and V once
+
+
+def load_traffic(name):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/r1d_traffic.json)."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "r1d_traffic.json")))[name]["bytes_per_launch"])
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -301,7 +316,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": units["bound"], "achieved": per_gpu, "peak": peak,
                          "unit": "TFLOP/s" if units["bound"] == "tensor" else "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "peak_source": peaks["source"] + (" burst" if units["bound"] == "tensor" else "")},
+                         "traffic": load_traffic(name) if not strong else None, "traffic_unit": "bytes per launch (ncu)",
+                         "algorithmic_bytes": algorithmic_bytes(name), "peak_source": peaks["source"] + (" burst" if units["bound"] == "tensor" else "")},
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(name, budget_s=args.cpu_budget)
