@@ -17,7 +17,7 @@ example: lib
 	  -I include -L build -lStarFlashAttention -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 oracle:
-	@echo "the oracle is Python (oracle/naive.py); nothing to compile"
+	$(MAKE) -C oracle
 
 clean:
 	rm -rf build starflashattention_b200/lib
