@@ -499,16 +499,20 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             uint32_t su[kCols];
             if constexpr (DBG != 2) {
 #pragma unroll
-                for (int c = 0; c < kCols / 2; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+                for (int c = 0; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+                // The buffer goes back the moment the loads have landed: its turnaround sits on the critical
+                // cycle of the pipeline (two query tiles share one score buffer at head_dim 128).
                 tmem_wait_ld();
-#pragma unroll
-                for (int c = kCols / 2; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
+                trace_event(tr, q, j, 9);
             }
             const int key0 = j * kBlockN;
             const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
                                    (key0 + kBlockN > p.seqlen_k);
             const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
-            // ---- row maximum: four independent chains, first half while the second half is in flight
+            // ---- row maximum: four independent chains
             float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
             auto scan_half = [&](int base) {
                 if (need_mask) {
@@ -521,13 +525,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
             };
             if constexpr (DBG != 2) scan_half(0);
-            tmem_wait_ld();
-            // the scores are in registers: hand the buffer back so that the next Q.K runs under this softmax
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
-            trace_event(tr, q, j, 9);
             if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
                 if (j > 0) ok = wait_barrier(bar_pv_done(q), (j - 1) & 1, p.error_flag, 8);
                 if (lane == 0) {
                     mbar_arrive(bar_p_ready(q, 0));
