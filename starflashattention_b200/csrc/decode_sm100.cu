@@ -15,10 +15,15 @@
 // each warp keeps a private online-softmax state (m, l, O) and the four states are merged through
 // shared memory at the end.
 //
-// Fragment trick: mma.sync.m16n8k16 with the query heads as the (zero padded) M rows.  A dot
-// product does not care about the order of its terms, so the head_dim axis is permuted such that
-// each thread's K fragment is one contiguous 16-byte load, and the output head_dim axis of P.V is
-// permuted such that each thread's V fragment comes from 16-byte loads too (two PRMTs per MMA).
+// Fragment trick: mma.sync.m16n8k16 fed straight from 16-byte global loads.  A dot product does not care about
+// the order of its terms, so the head_dim axis of Q.K is permuted such that each thread's K fragment is one
+// contiguous 16-byte load, and the head_dim axis of the P.V output is permuted such that each thread's V fragment
+// comes from 16-byte loads too (byte permutes pair up the keys).  The MMAs run TRANSPOSED (default, SWAP):
+// S^T = K Q^T puts 16 keys on the M rows and the (up to 8) query heads of the group on the 8 columns, and
+// O^T += V^T P^T puts 16 head_dim rows on M - every accumulator register is live, against half of them being the
+// zero padding of a 16-row query operand in the untransposed form (kept as SFA_DECODE_SWAP=0).  P changes from
+// accumulator to B-operand layout with one movmatrix per 8 keys.  Half the MMAs, 32 instead of 64 output
+// registers, 128 registers per thread, 4 CTAs per SM: C4 went from 5.77 to 6.49 TB/s.
 #include "internal.h"
 #include "merge.cuh"
 #include "rope.cuh"
@@ -31,6 +36,7 @@ namespace {
 
 constexpr int kWarps = 4;
 constexpr int kStepKeys = 16;
+constexpr bool kDecodeSwapDefault = true;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -99,6 +105,12 @@ struct DecodeParams {
     int force_partials;
 };
 
+// Kernel variant (read per call so the GPU tests can flip it): SFA_DECODE_SWAP=0 selects the untransposed MMAs.
+inline bool decode_swap_enabled() {
+    const char* e = getenv("SFA_DECODE_SWAP");
+    return e ? atoi(e) != 0 : kDecodeSwapDefault;
+}
+
 // Shared memory used only for the end-of-CTA merge of the four warp states.
 template <int D>
 struct MergeSmem {
@@ -107,8 +119,17 @@ struct MergeSmem {
     float l[kWarps][8];
 };
 
-template <typename T, int D, bool FUSED>
-__global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const DecodeParams p) {
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {   // transpose of an 8x8 b16 matrix held one row-pair per thread
+    uint32_t y;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
+    return y;
+}
+
+// SWAP: the MMAs run transposed - S^T = K Q^T (16 keys x 8 heads per MMA) and O^T += V^T P^T (16 head_dim rows x 8
+// heads) - so that every accumulator register is a live (key|dim, head) entry instead of half of them being the
+// zero padding of the 16-row query operand: half the MMAs, 32 instead of 64 output registers, 4 CTAs per SM.
+template <typename T, int D, bool FUSED, bool SWAP>
+__global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kernel(const DecodeParams p) {
     constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
     constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
     __shared__ MergeSmem<D> sm;
@@ -154,11 +175,13 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
         }
     }
 
-    float o_acc[NH * 8][4];
+    constexpr int NO = SWAP ? NH * 4 : NH * 8;
+    float o_acc[NO][4];
 #pragma unroll
-    for (int i = 0; i < NH * 8; ++i) { o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f; }
-    float m_run = -INFINITY;   // running max (log2 domain), identical across the quad
+    for (int i = 0; i < NO; ++i) { o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f; }
+    float m_run = -INFINITY;   // running max (log2 domain), identical across the quad (SWAP: head 2t, across r)
     float l_run = 0.f;         // this thread's share of the denominator
+    float m_run1 = -INFINITY, l_run1 = 0.f;   // SWAP only: head 2t + 1
 
     const T* kbase = reinterpret_cast<const T*>(p.k) + (int64_t)b * p.k_bs + (int64_t)hk * p.k_hs;
     const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)b * p.v_bs + (int64_t)hk * p.v_hs;
@@ -210,6 +233,50 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
             }
         }
 
+        if constexpr (SWAP) {
+            // ---- S^T = K Q^T: rows = keys base + {r, r + 8}, columns = heads {2t, 2t + 1}
+            float st[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                mma_16816<T>(st, kf[0][j].x, kf[1][j].x, kf[0][j].y, kf[1][j].y, qa[j][0], qa[j][1]);
+                mma_16816<T>(st, kf[0][j].z, kf[1][j].z, kf[0][j].w, kf[1][j].w, qa[j][2], qa[j][3]);
+            }
+            const bool dead0 = base + r >= k_end, dead1 = base + r + 8 >= k_end;
+            const float s0 = dead0 ? -INFINITY : st[0] * p.scale_log2, s1 = dead0 ? -INFINITY : st[1] * p.scale_log2;
+            const float s2 = dead1 ? -INFINITY : st[2] * p.scale_log2, s3 = dead1 ? -INFINITY : st[3] * p.scale_log2;
+            float mxa = fmaxf(s0, s2), mxb = fmaxf(s1, s3);
+#pragma unroll
+            for (int o = 4; o <= 16; o <<= 1) {
+                mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, o));
+                mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, o));
+            }
+            const float ma = fmaxf(m_run, mxa), mb = fmaxf(m_run1, mxb);   // finite: the step holds a live key
+            const float alpha_a = exp2f(m_run - ma), alpha_b = exp2f(m_run1 - mb);
+            const float p0 = exp2f(s0 - ma), p2 = exp2f(s2 - ma), p1 = exp2f(s1 - mb), p3 = exp2f(s3 - mb);
+            l_run = l_run * alpha_a + (p0 + p2);
+            l_run1 = l_run1 * alpha_b + (p1 + p3);
+            m_run = ma; m_run1 = mb;
+            if (__any_sync(0xffffffffu, alpha_a != 1.f || alpha_b != 1.f)) {
+#pragma unroll
+                for (int i = 0; i < NO; ++i) {
+                    o_acc[i][0] *= alpha_a; o_acc[i][2] *= alpha_a;
+                    o_acc[i][1] *= alpha_b; o_acc[i][3] *= alpha_b;
+                }
+            }
+            // ---- O^T += V^T P^T: P^T fragments are the transposed 8x8 blocks of the packed scores
+            const uint32_t pb0 = movmatrix_trans(pack2<T>(p0, p1));   // head r, keys 2t, 2t+1
+            const uint32_t pb1 = movmatrix_trans(pack2<T>(p2, p3));   // head r, keys 2t+8, 2t+9
+#pragma unroll
+            for (int h = 0; h < NH; ++h)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t w0 = u4_word(vf[0][h], i), w1 = u4_word(vf[1][h], i);
+                    const uint32_t w2 = u4_word(vf[2][h], i), w3 = u4_word(vf[3][h], i);
+                    mma_16816<T>(o_acc[h * 4 + i], __byte_perm(w0, w1, 0x5410u), __byte_perm(w0, w1, 0x7632u),
+                                 __byte_perm(w2, w3, 0x5410u), __byte_perm(w2, w3, 0x7632u), pb0, pb1);
+                }
+            return;
+        }
         // ---- S = Q K^T for two 8-key tiles
         float s[2][4];
 #pragma unroll
@@ -270,6 +337,27 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
     }
 
     // ---- merge the four warp states
+    if constexpr (SWAP) {
+#pragma unroll
+        for (int o = 4; o <= 16; o <<= 1) {
+            l_run += __shfl_xor_sync(0xffffffffu, l_run, o);
+            l_run1 += __shfl_xor_sync(0xffffffffu, l_run1, o);
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int hh = 2 * t + e;
+            if (hh < g) {
+                if (r == 0) { sm.m[warp][hh] = e ? m_run1 : m_run; sm.l[warp][hh] = e ? l_run1 : l_run; }
+#pragma unroll
+                for (int h = 0; h < NH; ++h)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        sm.o[warp][hh][64 * h + 8 * r + 2 * i] = o_acc[h * 4 + i][e];
+                        sm.o[warp][hh][64 * h + 8 * r + 2 * i + 1] = o_acc[h * 4 + i][2 + e];
+                    }
+            }
+        }
+    } else {
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
     l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
     if (r < g) {
@@ -280,6 +368,7 @@ __global__ void __launch_bounds__(kWarps * 32, 3) decode_splitkv_kernel(const De
             for (int i = 0; i < 8; ++i)
 #pragma unroll
                 for (int e = 0; e < 2; ++e) sm.o[warp][r][64 * h + 16 * t + 8 * e + i] = o_acc[h * 8 + i][e];
+    }
     }
     __syncthreads();
     for (int idx = threadIdx.x; idx < g * D; idx += kWarps * 32) {
@@ -329,8 +418,13 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
     dim3 grid(a.num_splits, a.heads_kv, a.batch);
-    if (a.fused_qkv) decode_splitkv_kernel<T, D, true><<<grid, kWarps * 32, 0, stream>>>(p);
-    else decode_splitkv_kernel<T, D, false><<<grid, kWarps * 32, 0, stream>>>(p);
+    if (decode_swap_enabled()) {
+        if (a.fused_qkv) decode_splitkv_kernel<T, D, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
+        else decode_splitkv_kernel<T, D, false, true><<<grid, kWarps * 32, 0, stream>>>(p);
+    } else {
+        if (a.fused_qkv) decode_splitkv_kernel<T, D, true, false><<<grid, kWarps * 32, 0, stream>>>(p);
+        else decode_splitkv_kernel<T, D, false, false><<<grid, kWarps * 32, 0, stream>>>(p);
+    }
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     if (a.num_splits > 1 && !a.force_partials) {
@@ -353,7 +447,9 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
         return w > 0 ? w : 4;
     }();
     const long units = (long)batch * heads_kv;
-    const long slots = (long)sm_count * 3 * waves;
+    const char* ce = getenv("SFA_DECODE_CTAS");
+    const int ctas_per_sm = ce && atoi(ce) > 0 ? atoi(ce) : 3;
+    const long slots = (long)sm_count * ctas_per_sm * waves;
     long s = (slots + units - 1) / units;
     const long max_by_len = max_seqlen / 256 > 0 ? max_seqlen / 256 : 1;
     if (s > max_by_len) s = max_by_len;

@@ -8,7 +8,7 @@
 
 namespace sfa {
 
-constexpr int kMergeGroups = 4;   // blockDim.x = D * kMergeGroups; thread = (group g, head_dim element d)
+constexpr int kMergeGroups = 8;   // blockDim.x = D * kMergeGroups; thread = (group g, head_dim element d)
 
 template <int D>
 struct MergeScratch {
@@ -55,14 +55,18 @@ __device__ __forceinline__ void merge_splits(const float* __restrict__ o_part, c
     __syncthreads();                      // also publishes w_sm
     l = lane < W ? sc.red[lane] : 0.f;
     L = warp_sum(l);
-    float a0 = 0.f, a1 = 0.f;
+    // four independent loads in flight per thread: with a few hundred splits the loop is latency bound
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     const float* op = o_part + row0 * D + d;
+    constexpr int G = kMergeGroups;
     int s = g;
-    for (; s + kMergeGroups < S; s += 2 * kMergeGroups) {
-        a0 += w_sm[s] * op[(int64_t)s * D];
-        a1 += w_sm[s + kMergeGroups] * op[(int64_t)(s + kMergeGroups) * D];
+    for (; s + 3 * G < S; s += 4 * G) {
+        const float v0 = op[(int64_t)s * D], v1 = op[(int64_t)(s + G) * D];
+        const float v2 = op[(int64_t)(s + 2 * G) * D], v3 = op[(int64_t)(s + 3 * G) * D];
+        a0 += w_sm[s] * v0; a1 += w_sm[s + G] * v1; a2 += w_sm[s + 2 * G] * v2; a3 += w_sm[s + 3 * G] * v3;
     }
-    if (s < S) a0 += w_sm[s] * op[(int64_t)s * D];
+    for (; s < S; s += G) a0 += w_sm[s] * op[(int64_t)s * D];
+    a0 += a2; a1 += a3;
     sc.acc[g][d] = a0 + a1;
     __syncthreads();
     acc = 0.f;

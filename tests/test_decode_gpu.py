@@ -59,6 +59,21 @@ def test_decode_matches_oracle(dtype, B, Hq, Hkv, D, M, lens, splits):
     assert float((lse[fin] - lse_ref[fin]).abs().max() if fin.any() else 0.0) <= 1e-3
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_decode_untransposed_variant_matches_oracle(dtype, monkeypatch):
+    """SFA_DECODE_SWAP=0: the untransposed MMA form of the split-KV kernel (query heads on the M rows)."""
+    import starflashattention_b200 as sfa
+    monkeypatch.setenv("SFA_DECODE_SWAP", "0")
+    B, Hq, Hkv, D, M = 2, 8, 2, 128, 1500
+    q, kc, vc = _rand((B, Hq, D), dtype, 81), _rand((B, M, Hkv, D), dtype, 82), _rand((B, M, Hkv, D), dtype, 83)
+    seqlens = torch.tensor([1500, 333], dtype=torch.int32)
+    o_ref, lse_ref = naive.decode_attention(q, kc, vc, seqlens)
+    o, lse = sfa.decode(q.cuda(), kc.cuda(), vc.cuda(), seqlens.cuda(), num_splits=3)
+    torch.cuda.synchronize()
+    _assert_close(o, o_ref, dtype, "O")
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+
+
 def test_decode_strided_cache_and_no_seqlens():
     """Caches that are views into a (B, L, M, H, D) table (the drop-in layout), seqlens = None."""
     import starflashattention_b200 as sfa
