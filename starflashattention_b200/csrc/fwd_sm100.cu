@@ -5,20 +5,20 @@
 //
 // Structure (one CTA per NQ x 128 query rows of one (batch, head)):
 //   warps 0 .. 4*NQ-1   softmax warpgroups, one per 128-row query tile; thread i of a warpgroup owns
-//                       row i (TMEM lane i): tcgen05.ld S -> online softmax in fp32 (exp2 on
-//                       log2e-prescaled scores, fused causal/tail masking) -> tcgen05.st P as
-//                       bf16/fp16 over the S columns -> epilogue O / l -> global
+//                       row i (TMEM lane i): tcgen05.ld S -> score buffer handed back -> online softmax
+//                       in fp32 (exp2 on log2e-prescaled scores, fused causal/tail masking) ->
+//                       tcgen05.st P as bf16/fp16 into the tile's own P columns -> epilogue O / l -> global
 //   warp 4*NQ           TMA producer: Q tiles once, then K_0 V_0 K_1 V_1 ... through a ring of
 //                       128-key tiles in shared memory (128-byte swizzle), mbarrier full/empty
-//   warp 4*NQ+1         tcgen05 issuer (one thread): S_q = Q_q K_j^T (SS, both operands K-major) and
-//                       O_q += P_q V_j (TS: A = P in TMEM, B = V in smem, MN-major); it also owns
-//                       the TMEM allocation
+//   warps 4*NQ+1 ..     tcgen05 issuers, one warp per query tile (one elected lane issues):
+//                       S_q = Q_q K_j^T (SS, both operands K-major) and O_q += P_q V_j (TS: A = P in
+//                       TMEM, B = V in smem, MN-major); the first of them owns the TMEM allocation
 // TMEM: P0 P1 | S | O0 O1 = 2 x 64 + 128 + 2 x 128 columns at head_dim 128.  P does not alias S: a
 // softmax warpgroup frees the score buffer as soon as its tcgen05.ld has landed in registers, so
 // the tensor pipe computes S(q, j+1) while the warpgroup is still exponentiating tile j.  The
 // softmax warpgroups therefore run back to back (throughput bound) instead of sitting in the
-// latency chain softmax -> P.V -> Q.K(next) of an aliased S/P layout.  Issue order of the MMA warp:
-// step (q, j), j-major: Q.K(q, j) then P.V(q, j-1).  The single score buffer alternates between
+// latency chain softmax -> P.V -> Q.K(next) of an aliased S/P layout.  Issue order of tile q's MMA warp:
+// Q.K(q, j) then P.V(q, j-1), for j = 0, 1, ...  The single score buffer alternates between
 // the two query tiles (head_dim 64 and the one-tile variant have room for two buffers).
 // O is rescaled lazily: the reference maximum of a row only moves when the true maximum has grown
 // by more than 2^8, so the TMEM read-modify-write of O is rare after the first tiles.
@@ -41,6 +41,7 @@ constexpr int kBlockN = 128;        // keys per tile
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;   // log2 units
+constexpr int kStaggerCycles64 = 0;         // head start of softmax warpgroup 0 at head_dim 64 (cycles)
 
 struct FwdParams {
     void* o;
@@ -50,6 +51,7 @@ struct FwdParams {
     int seqlen_q, seqlen_k, heads_q, group;
     int causal, is_bf16;
     float scale_log2;
+    int stagger_cycles;   // head start of warpgroup 0 over warpgroup 1 (see launch_fwd)
 };
 
 __device__ int g_fwd_error;
@@ -488,6 +490,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         const bool probe = DBG == 5 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
         long long pt_wait = 0, pt_max = 0, pt_exp = 0, pt_pv = 0, pt0 = 0, pt1 = 0, pt2 = 0;
         const bool tr = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
+        // With a score buffer of their own (head_dim 64) nothing couples the two warpgroups, and started together
+        // they stay in lockstep: both in the exp2 loop (MUFU contended), then both in the load + max phase (MUFU
+        // idle).  A head start for warpgroup 0 puts one's exp2 loop under the other's max phase.
+        if (NQ == 2 && q == 1 && p.stagger_cycles > 0) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < p.stagger_cycles) __nanosleep(64);
+        }
         for (int j = 0; j < (kFreeRun ? 0 : n_q) && ok; ++j) {
             if constexpr (DBG == 5) pt0 = clock64();
             const int buf = s_buffer(q, j);
@@ -833,6 +842,10 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
     p.causal = a.causal ? 1 : 0; p.is_bf16 = a.dtype == SFA_BF16;
     const float scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
     p.scale_log2 = scale * kLog2e;
+    {
+        const char* e = getenv("SFA_FWD_STAGGER");
+        p.stagger_cycles = e ? atoi(e) : (a.head_dim == 64 ? kStaggerCycles64 : 0);
+    }
     void* flag_addr = nullptr;
     SFA_CUDA_CHECK(cudaGetSymbolAddress(&flag_addr, g_fwd_error));
     p.error_flag = reinterpret_cast<int*>(flag_addr);
