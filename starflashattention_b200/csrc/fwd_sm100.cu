@@ -41,7 +41,10 @@ constexpr int kBlockN = 128;        // keys per tile
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kRescaleThreshold = 8.0f;   // log2 units
-constexpr int kStaggerCycles64 = 0;         // head start of softmax warpgroup 0 at head_dim 64 (cycles)
+// Head start of softmax warpgroup 0 at head_dim 64 (cycles): with a score buffer each, the two warpgroups otherwise
+// run in lockstep (both on the MUFU, then both off it).  Measured on five shapes (profiles/r1_fwd_tuning.md):
+// 1700 cycles is +0.4 % .. +4.2 %, never a loss.
+constexpr int kStaggerCycles64 = 1700;
 
 struct FwdParams {
     void* o;
