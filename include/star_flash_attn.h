@@ -100,6 +100,25 @@ int sfa_decode(const sfa_decode_args* args, void* stream);
 int sfa_decode_num_splits(const sfa_decode_args* args);
 size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits);
 
+/* ---------------------------------------------------------------- split-KV decode over a paged cache ---
+ * Row f1 of the scope table ("a paged/strided KV-cache layout"); the reference documents one
+ * dense (batch, layer, max_len, heads, head_dim) cache (src/params.h:22-25) and has no paged form.
+ * `base.k_cache` / `base.v_cache` are page POOLS (num_pages, page_size, heads_kv, head_dim) whose
+ * `*_batch_stride` fields carry the PAGE stride in elements; block_table (batch, block_table_stride) int32 names
+ * the pool page that holds keys [i * page_size, (i + 1) * page_size) of sequence b at [b][i]; page_size is a
+ * power of two >= 16; `base.seqlen_k` is the largest addressable length (at most block_table columns * page_size)
+ * and `base.seqlens` the visible length per sequence.  Same kernel, same split/merge arithmetic as sfa_decode:
+ * with equal num_splits the result is bit-identical to sfa_decode over the gathered cache. */
+typedef struct sfa_decode_paged_args {
+    sfa_decode_args base;
+    const int32_t* block_table;
+    int64_t block_table_stride;
+    int32_t page_size;
+    int32_t num_pages; /* pool size; > 0.  Table entries are trusted to lie in [0, num_pages). */
+} sfa_decode_paged_args;
+
+int sfa_decode_paged(const sfa_decode_paged_args* args, void* stream);
+
 /* ---------------------------------------------------------------- cross-GPU split-KV decode ---
  * One long sequence whose KV length is sharded over the GPUs of a box (one process per GPU).  Every rank
  * calls sfa_decode_sharded with ITS shard as k_cache/v_cache (seqlen_k = shard length, seqlens = number of

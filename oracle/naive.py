@@ -130,6 +130,15 @@ def decode_attention(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tens
     return torch.stack(outs), torch.stack(lses)
 
 
+def gather_pages(pool: torch.Tensor, block_table: torch.Tensor) -> torch.Tensor:
+    """Paged cache -> the dense (B, blocks * page_size, Hkv, D) cache it stands for: pool (pages, page_size, Hkv, D),
+    block_table (B, blocks) of pool pages.  The reference has no paged cache (its layout is the dense one of
+    src/params.h:22-25); this is the definition the paged kernel is checked against."""
+    B, blocks = block_table.shape
+    _, ps, Hkv, D = pool.shape
+    return pool[block_table.long().reshape(-1)].reshape(B, blocks * ps, Hkv, D)
+
+
 def decode_step_reference(qkv: torch.Tensor, k_cache_table: torch.Tensor,
                           v_cache_table: torch.Tensor, seq_len: torch.Tensor, idx_layer: int,
                           rotary_dim: Optional[int] = None,

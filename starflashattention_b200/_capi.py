@@ -16,7 +16,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
+    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -58,6 +58,13 @@ class DecodeArgs(C.Structure):
     ]
 
 
+class DecodePagedArgs(C.Structure):
+    _fields_ = [
+        ("base", DecodeArgs), ("block_table", C.c_void_p), ("block_table_stride", C.c_int64),
+        ("page_size", C.c_int32), ("num_pages", C.c_int32),
+    ]
+
+
 class DecoderStepArgs(C.Structure):
     _fields_ = [
         ("qkv", C.c_void_p), ("o", C.c_void_p), ("seq_len", C.c_void_p),
@@ -93,6 +100,8 @@ def _load() -> C.CDLL:
     lib.sfa_fwd.restype = C.c_int
     lib.sfa_decode.argtypes = [C.POINTER(DecodeArgs), C.c_void_p]
     lib.sfa_decode.restype = C.c_int
+    lib.sfa_decode_paged.argtypes = [C.POINTER(DecodePagedArgs), C.c_void_p]
+    lib.sfa_decode_paged.restype = C.c_int
     lib.sfa_decode_num_splits.argtypes = [C.POINTER(DecodeArgs)]
     lib.sfa_decode_num_splits.restype = C.c_int
     lib.sfa_decode_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32]

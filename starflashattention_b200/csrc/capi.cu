@@ -29,7 +29,12 @@ struct FusedStep {   // new-token inputs of the fused decoder step (see DecodeLa
     int64_t qkv_stride; int rotary_dim;
 };
 
-int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream, const FusedStep* fused = nullptr) {
+struct PagedKV {
+    const int32_t* block_table; int64_t bt_stride; int page_size;
+};
+
+int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream, const FusedStep* fused = nullptr,
+                const PagedKV* paged = nullptr) {
     int rc = check_dtype(a.dtype);
     if (rc) return rc;
     if ((!a.q && !fused) || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "decode: null tensor pointer");
@@ -63,6 +68,7 @@ int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream, c
         L.fused_qkv = fused->qkv; L.cos_table = fused->cos_table; L.sin_table = fused->sin_table;
         L.qkv_stride = fused->qkv_stride; L.rotary_dim = fused->rotary_dim;
     }
+    if (paged) { L.block_table = paged->block_table; L.bt_stride = paged->bt_stride; L.page_size = paged->page_size; }
     if (L.num_splits > 1) {
         const size_t need = decode_workspace_bytes(a.batch, a.heads_q, a.head_dim, L.num_splits);
         uint8_t* ws = reinterpret_cast<uint8_t*>(a.workspace);
@@ -233,6 +239,19 @@ int sfa_fwd(const sfa_fwd_args* args, void* stream) {
 int sfa_decode(const sfa_decode_args* args, void* stream) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode: null args");
     return sfa::decode_impl(*args, 0, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode_paged(const sfa_decode_paged_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_paged: null args");
+    if (!args->block_table) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_paged: null block table");
+    const int ps = args->page_size;
+    if (ps < 16 || (ps & (ps - 1))) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_paged: page_size must be a power of two >= 16");
+    if (args->num_pages <= 0) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_paged: num_pages must be positive");
+    const int64_t blocks = ((int64_t)args->base.seqlen_k + ps - 1) / ps;
+    if (args->block_table_stride < blocks)
+        return sfa::fail(SFA_ERR_INVALID, "sfa_decode_paged: block table rows are shorter than seqlen_k / page_size");
+    const sfa::PagedKV pk = {args->block_table, args->block_table_stride, ps};
+    return sfa::decode_impl(args->base, 0, reinterpret_cast<cudaStream_t>(stream), nullptr, &pk);
 }
 
 int sfa_decode_num_splits(const sfa_decode_args* args) {

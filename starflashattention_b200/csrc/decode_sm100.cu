@@ -103,6 +103,11 @@ struct DecodeParams {
     int64_t qkv_stride;
     int rotary_dim, heads_kv;
     int force_partials;
+    // paged cache (PAGED kernels only): k / v are page pools (pages, page_size, heads_kv, D) with k_bs / v_bs the
+    // page stride; block_table[b * bt_stride + i] is the pool page holding keys [i, i + 1) << page_shift of sequence b
+    const int32_t* block_table;
+    int64_t bt_stride;
+    int page_shift;
 };
 
 // Kernel variant (read per call so the GPU tests can flip it): SFA_DECODE_SWAP=0 selects the untransposed MMAs.
@@ -128,7 +133,10 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {   // transpose
 // SWAP: the MMAs run transposed - S^T = K Q^T (16 keys x 8 heads per MMA) and O^T += V^T P^T (16 head_dim rows x 8
 // heads) - so that every accumulator register is a live (key|dim, head) entry instead of half of them being the
 // zero padding of the 16-row query operand: half the MMAs, 32 instead of 64 output registers, 4 CTAs per SM.
-template <typename T, int D, bool FUSED, bool SWAP>
+// PAGED: the cache is a pool of pages found through a per-sequence block table.  A 16-key step never straddles a
+// page (page_size is a power of two >= 16 and chunks start on multiples of 64), so the indirection is one
+// warp-uniform table read per step; everything after the row pointer is the same streaming code.
+template <typename T, int D, bool FUSED, bool SWAP, bool PAGED = false>
 __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kernel(const DecodeParams p) {
     constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
     constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
@@ -183,11 +191,10 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     float l_run = 0.f;         // this thread's share of the denominator
     float m_run1 = -INFINITY, l_run1 = 0.f;   // SWAP only: head 2t + 1
 
-    const T* kbase = reinterpret_cast<const T*>(p.k) + (int64_t)b * p.k_bs + (int64_t)hk * p.k_hs;
-    const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)b * p.v_bs + (int64_t)hk * p.v_hs;
+    const T* kbase = reinterpret_cast<const T*>(p.k) + (PAGED ? 0 : (int64_t)b * p.k_bs) + (int64_t)hk * p.k_hs;
+    const T* vbase = reinterpret_cast<const T*>(p.v) + (PAGED ? 0 : (int64_t)b * p.v_bs) + (int64_t)hk * p.v_hs;
+    const int32_t* bt = PAGED ? p.block_table + (int64_t)b * p.bt_stride : nullptr;
 
-    T* kcache = const_cast<T*>(kbase);   // FUSED: the cache is appended to
-    T* vcache = const_cast<T*>(vbase);
     // One 16-key step of this warp.  NEW (fused step only): the step holds the appended token, whose k (rotated
     // here) and v come from `qkv` instead of the cache and are written to the cache row `pos` by the threads
     // whose fragment is that row.
@@ -196,13 +203,26 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
         const int last = k_end - 1;
         const T* tok_k = NEW ? token_row(p.heads_q + hk) : nullptr;
         const T* tok_v = NEW ? token_row(p.heads_q + p.heads_kv + hk) : nullptr;
+        // rows of this step: cache row `key` is kb + (key - key0) * k_rs (paged: inside the step's page)
+        const T* kb = kbase;
+        const T* vb = vbase;
+        int key0 = 0;
+        if constexpr (PAGED) {
+            const int blk = base >> p.page_shift;
+            const int64_t page = bt[blk];
+            key0 = blk << p.page_shift;
+            kb = kbase + page * p.k_bs;
+            vb = vbase + page * p.v_bs;
+        }
+        T* kcache = const_cast<T*>(kb);   // FUSED: the cache is appended to
+        T* vcache = const_cast<T*>(vb);
         // ---- issue every load of the step up front (16 x 16 B per thread at D=128)
         uint4 kf[2][NJ];
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
             const int key = min(base + 8 * nt + r, last);
             const bool from_tok = NEW && key == pos;
-            const T* row = (from_tok ? tok_k : kbase + (int64_t)key * p.k_rs) + 8 * t;
+            const T* row = (from_tok ? tok_k : kb + (int64_t)(key - key0) * p.k_rs) + 8 * t;
 #pragma unroll
             for (int j = 0; j < NJ; ++j) kf[nt][j] = ld_stream(row + 32 * j);
             if constexpr (NEW) {
@@ -211,7 +231,7 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
                     for (int j = 0; j < NJ; ++j) {
                         kf[nt][j] = rope_rotate8<T>(kf[nt][j], 32 * j + 8 * t, pos, p.rotary_dim, p.cos_table, p.sin_table);
                         if (base + 8 * nt + r == pos)   // the unclamped owner of the row appends it
-                            *reinterpret_cast<uint4*>(kcache + (int64_t)pos * p.k_rs + 32 * j + 8 * t) = kf[nt][j];
+                            *reinterpret_cast<uint4*>(kcache + (int64_t)(pos - key0) * p.k_rs + 32 * j + 8 * t) = kf[nt][j];
                     }
                 }
             }
@@ -222,13 +242,13 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
             const int key_raw = base + 2 * t + (kk & 1) + 8 * (kk >> 1);
             const int key = min(key_raw, last);
             const bool from_tok = NEW && key == pos;
-            const T* row = (from_tok ? tok_v : vbase + (int64_t)key * p.v_rs) + 8 * r;
+            const T* row = (from_tok ? tok_v : vb + (int64_t)(key - key0) * p.v_rs) + 8 * r;
 #pragma unroll
             for (int h = 0; h < NH; ++h) {
                 vf[kk][h] = ld_stream(row + 64 * h);
                 if constexpr (NEW) {
                     if (from_tok && key_raw == pos)
-                        *reinterpret_cast<uint4*>(vcache + (int64_t)pos * p.v_rs + 8 * r + 64 * h) = vf[kk][h];
+                        *reinterpret_cast<uint4*>(vcache + (int64_t)(pos - key0) * p.v_rs + 8 * r + 64 * h) = vf[kk][h];
                 }
             }
         }
@@ -418,7 +438,9 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
     dim3 grid(a.num_splits, a.heads_kv, a.batch);
-    if (decode_swap_enabled()) {
+    if (a.block_table) {
+        decode_splitkv_kernel<T, D, false, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
+    } else if (decode_swap_enabled()) {
         if (a.fused_qkv) decode_splitkv_kernel<T, D, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
         else decode_splitkv_kernel<T, D, false, true><<<grid, kWarps * 32, 0, stream>>>(p);
     } else {
@@ -470,6 +492,11 @@ int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     if (g > 8) return fail(SFA_ERR_UNSUPPORTED, "decode supports heads_q / heads_kv <= 8");
     if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
     if (a.batch == 0) return SFA_OK;
+    if (a.block_table) {
+        if (a.fused_qkv) return fail(SFA_ERR_UNSUPPORTED, "the fused decoder step does not take a paged cache");
+        if (a.page_size < kStepKeys || (a.page_size & (a.page_size - 1)))
+            return fail(SFA_ERR_INVALID, "page_size must be a power of two >= 16");
+    }
     DecodeParams p;
     p.q = a.q; p.k = a.k; p.v = a.v; p.seqlens = a.seqlens; p.o = a.o; p.lse = a.lse;
     p.o_part = a.o_part; p.ml_part = a.ml_part;
@@ -480,6 +507,8 @@ int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     p.scale_log2 = a.scale * kLog2e;
     p.qkv = a.fused_qkv; p.cos_table = a.cos_table; p.sin_table = a.sin_table; p.qkv_stride = a.qkv_stride;
     p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv; p.force_partials = a.force_partials ? 1 : 0;
+    p.block_table = a.block_table; p.bt_stride = a.bt_stride; p.page_shift = 0;
+    while (a.block_table && (1 << p.page_shift) < a.page_size) ++p.page_shift;
     if (a.dtype == SFA_FP16) {
         return a.head_dim == 128 ? launch_typed<__half, 128>(a, p, stream) : launch_typed<__half, 64>(a, p, stream);
     }

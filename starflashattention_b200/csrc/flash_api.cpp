@@ -129,6 +129,43 @@ std::tuple<at::Tensor, at::Tensor> decode(const at::Tensor& q, const at::Tensor&
     return {out, lse};
 }
 
+// Decode over a paged cache: pools (pages, page_size, heads_kv, head_dim), block_table int32 (batch, blocks).
+std::tuple<at::Tensor, at::Tensor> decode_paged(const at::Tensor& q, const at::Tensor& k_pool, const at::Tensor& v_pool,
+                                                const at::Tensor& block_table, const at::Tensor& seqlens,
+                                                double softmax_scale, int num_splits) {
+    TORCH_CHECK(q.is_cuda() && k_pool.is_cuda() && v_pool.is_cuda() && block_table.is_cuda() && seqlens.is_cuda(),
+                "star_flash_attn.decode_paged: CUDA tensors required");
+    TORCH_CHECK(q.dim() == 3 && k_pool.dim() == 4 && k_pool.sizes() == v_pool.sizes() && k_pool.size(3) == q.size(2),
+                "q must be (batch, heads, head_dim); pools (pages, page_size, heads_kv, head_dim)");
+    TORCH_CHECK(q.stride(2) == 1 && k_pool.stride(3) == 1 && v_pool.stride(3) == 1, "the head_dim axis must be contiguous");
+    TORCH_CHECK(q.scalar_type() == k_pool.scalar_type() && q.scalar_type() == v_pool.scalar_type(), "dtype mismatch");
+    TORCH_CHECK(block_table.scalar_type() == at::kInt && block_table.dim() == 2 && block_table.size(0) == q.size(0) &&
+                    block_table.stride(1) == 1, "block_table must be int32 (batch, blocks) with contiguous rows");
+    TORCH_CHECK(seqlens.scalar_type() == at::kInt && seqlens.is_contiguous() && seqlens.numel() == q.size(0),
+                "seqlens must be a contiguous int32 CUDA tensor of shape (batch,)");
+    c10::cuda::CUDAGuard guard(q.device());
+    at::Tensor out = at::empty(q.sizes(), q.options());
+    at::Tensor lse = at::empty({q.size(0), q.size(1)}, q.options().dtype(at::kFloat));
+    sfa_decode_paged_args p{};
+    sfa_decode_args& a = p.base;
+    a.q = q.data_ptr(); a.k_cache = k_pool.data_ptr(); a.v_cache = v_pool.data_ptr();
+    a.seqlens = seqlens.data_ptr<int>();
+    a.o = out.data_ptr(); a.lse = lse.data_ptr<float>();
+    a.batch = (int)q.size(0); a.seqlen_k = (int)(block_table.size(1) * k_pool.size(1));
+    a.heads_q = (int)q.size(1); a.heads_kv = (int)k_pool.size(2); a.head_dim = (int)q.size(2);
+    a.q_batch_stride = q.stride(0); a.q_head_stride = q.stride(1);
+    a.k_batch_stride = k_pool.stride(0); a.k_row_stride = k_pool.stride(1); a.k_head_stride = k_pool.stride(2);
+    a.v_batch_stride = v_pool.stride(0); a.v_row_stride = v_pool.stride(1); a.v_head_stride = v_pool.stride(2);
+    a.o_batch_stride = out.stride(0); a.o_head_stride = out.stride(1);
+    a.softmax_scale = (float)softmax_scale;
+    a.num_splits = num_splits;
+    a.dtype = dtype_code(q);
+    p.block_table = block_table.data_ptr<int>(); p.block_table_stride = block_table.stride(0);
+    p.page_size = (int)k_pool.size(1); p.num_pages = (int)k_pool.size(0);
+    check_rc(sfa_decode_paged(&p, current_stream()));
+    return {out, lse};
+}
+
 PYBIND11_MODULE(star_flash_attn, m) {
     m.doc() = "B200-native FlashAttention forward and split-KV decode behind StarFlashAttention's Python entry point";
     m.def("mha_fwd_cuda", &mha_fwd_cuda, "One decoder step: RoPE + KV-cache append + split-KV attention (in-place on o)",
@@ -140,5 +177,8 @@ PYBIND11_MODULE(star_flash_attn, m) {
           py::arg("causal") = false, py::arg("softmax_scale") = 0.0);
     m.def("decode", &decode, "Split-KV decode attention: returns (out, lse)", py::arg("q"), py::arg("k_cache"),
           py::arg("v_cache"), py::arg("seqlens") = c10::nullopt, py::arg("softmax_scale") = 0.0, py::arg("num_splits") = 0);
+    m.def("decode_paged", &decode_paged, "Split-KV decode attention over a paged cache: returns (out, lse)", py::arg("q"),
+          py::arg("k_pool"), py::arg("v_pool"), py::arg("block_table"), py::arg("seqlens"), py::arg("softmax_scale") = 0.0,
+          py::arg("num_splits") = 0);
     m.def("launch_count", []() { return (uint64_t)sfa_launch_count(); });
 }

@@ -54,6 +54,11 @@ struct DecodeLaunch {
     int64_t qkv_stride = 0;
     int rotary_dim = 0;
     bool force_partials = false;   // write (o_part, ml_part) even with one split (cross-GPU sharded decode)
+    // Paged cache (nullptr = contiguous): k / v are page pools, k_bs / v_bs the page strides, block_table
+    // (batch, bt_stride) int32 maps the i-th page_size-key block of a sequence to its pool page.
+    const int32_t* block_table = nullptr;
+    int64_t bt_stride = 0;
+    int page_size = 0;
 };
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count);
 size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits);

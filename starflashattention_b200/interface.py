@@ -18,7 +18,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _capi
-from ._capi import DecodeArgs, DecoderStepArgs, FwdArgs, check, lib
+from ._capi import DecodeArgs, DecodePagedArgs, DecoderStepArgs, FwdArgs, check, lib
 
 __all__ = ["DecoderStepGraph", "fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
            "launch_count", "decode_num_splits"]
@@ -135,6 +135,43 @@ def decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     a = _decode_args(q, k_cache, v_cache, seqlens, out, lse, softmax_scale, num_splits)
     with torch.cuda.device(dev):
         check(lib.sfa_decode(a, _stream()))
+    return out, lse
+
+
+def decode_paged(q: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor,
+                 seqlens: torch.Tensor, softmax_scale: Optional[float] = None, num_splits: int = 0,
+                 out: Optional[torch.Tensor] = None,
+                 return_lse: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Single-token attention over a PAGED KV cache (scope row f1).  q (B,Hq,D); pools (pages, page_size, Hkv, D);
+    block_table int32 (B, blocks): pool page of each page_size-key block of a sequence; seqlens int32 (B) visible
+    keys, at most blocks * page_size.  Same kernel and arithmetic as :func:`decode`."""
+    dev = _require_cuda(q, k_pool, v_pool, block_table, seqlens, out)
+    if q.dim() != 3 or k_pool.dim() != 4 or v_pool.shape != k_pool.shape:
+        raise ValueError("q must be (batch, heads, head_dim); pools (pages, page_size, heads_kv, head_dim)")
+    if q.shape[2] != k_pool.shape[3]:
+        raise ValueError("head_dim mismatch between q and the pools")
+    if q.dtype != k_pool.dtype or q.dtype != v_pool.dtype:
+        raise TypeError("q and the pools must share one dtype")
+    for t in (q, k_pool, v_pool):
+        if t.stride(-1) != 1:
+            raise ValueError("the head_dim axis must be contiguous")
+    if block_table.dtype != torch.int32 or block_table.dim() != 2 or block_table.shape[0] != q.shape[0] or \
+            block_table.stride(1) != 1:
+        raise ValueError("block_table must be int32 (batch, blocks) with contiguous rows")
+    if seqlens is None or seqlens.dtype != torch.int32 or seqlens.numel() != q.shape[0] or not seqlens.is_contiguous():
+        raise ValueError("seqlens must be a contiguous int32 tensor of shape (batch,)")
+    if out is None:
+        out = torch.empty_like(q, memory_format=torch.contiguous_format)
+    elif out.shape != q.shape or out.dtype != q.dtype or out.stride(-1) != 1:
+        raise ValueError("out must look like q")
+    lse = torch.empty(q.shape[:2], dtype=torch.float32, device=dev) if return_lse else None
+    pa = DecodePagedArgs()
+    pa.base = _decode_args(q, k_pool, v_pool, seqlens, out, lse, softmax_scale, num_splits)
+    pa.base.seqlen_k = block_table.shape[1] * k_pool.shape[1]      # largest addressable length
+    pa.block_table, pa.block_table_stride = block_table.data_ptr(), block_table.stride(0)
+    pa.page_size, pa.num_pages = k_pool.shape[1], k_pool.shape[0]
+    with torch.cuda.device(dev):
+        check(lib.sfa_decode_paged(pa, _stream()))
     return out, lse
 
 

@@ -41,6 +41,7 @@ def test_abi_version_and_struct_sizes(built_library):
     # offsets implied by include/star_flash_attn.h (LP64): 5 pointers, 6 int32, 12 int64, float + 2 int32 (+pad)
     assert ctypes.sizeof(_capi.FwdArgs) == 5 * 8 + 6 * 4 + 12 * 8 + 4 + 2 * 4 + 4
     assert ctypes.sizeof(_capi.DecodeArgs) == 6 * 8 + 5 * 4 + 4 + 10 * 8 + 3 * 4 + 4 + 8 + 8
+    assert ctypes.sizeof(_capi.DecodePagedArgs) == ctypes.sizeof(_capi.DecodeArgs) + 8 + 8 + 4 + 4
     assert ctypes.sizeof(_capi.DecoderStepArgs) == 8 * 8 + 4 * 4 + 4 + 6 * 4 + 4
 
 
@@ -66,6 +67,15 @@ def test_argument_validation_without_gpu(built_library):
     d.dtype = 7
     assert lib.sfa_decode(d, None) == _capi.SFA_ERR_INVALID
     assert lib.sfa_decode_workspace_bytes(8, 32, 128, 1) == 0
+    pg = _capi.DecodePagedArgs()
+    assert lib.sfa_decode_paged(None, None) == _capi.SFA_ERR_INVALID
+    assert lib.sfa_decode_paged(pg, None) == _capi.SFA_ERR_INVALID       # null block table
+    pg.block_table, pg.num_pages, pg.block_table_stride = p, 4, 1
+    for bad in (0, 8, 24, 48):
+        pg.page_size = bad
+        assert lib.sfa_decode_paged(pg, None) == _capi.SFA_ERR_INVALID and b"page_size" in lib.sfa_last_error()
+    pg.page_size, pg.base.seqlen_k = 16, 64                              # 4 blocks needed, rows hold 1
+    assert lib.sfa_decode_paged(pg, None) == _capi.SFA_ERR_INVALID and b"block table" in lib.sfa_last_error()
     assert lib.sfa_decode_workspace_bytes(8, 32, 128, 16) >= 8 * 32 * 16 * (128 * 4 + 8)
 
 

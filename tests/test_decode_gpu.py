@@ -104,6 +104,99 @@ def test_decode_split_counts_agree():
         assert float((l - l1).abs().max()) <= 1e-4
 
 
+def _paged_case(dtype, B, Hkv, D, page, blocks, seed):
+    """A pool with more pages than the sequences use, and a block table that scatters every sequence over it."""
+    g = torch.Generator().manual_seed(seed)
+    pages = B * blocks + 5
+    k_pool = _rand((pages, page, Hkv, D), dtype, seed + 1)
+    v_pool = _rand((pages, page, Hkv, D), dtype, seed + 2)
+    table = torch.randperm(pages, generator=g)[:B * blocks].reshape(B, blocks).to(torch.int32)
+    return k_pool, v_pool, table
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("B,Hq,Hkv,D,page,blocks,lens,splits", [
+    (2, 8, 2, 128, 16, 40, [640, 333], 0),       # smallest page: one 16-key step per page
+    (3, 8, 1, 128, 64, 11, [1, 64, 700], 5),     # GQA 8, one-key sequence, page boundary, odd split count
+    (2, 4, 2, 64, 128, 5, [513, 17], 3),         # head_dim 64
+    (2, 2, 2, 128, 256, 2, [0, 512], 4),         # an empty sequence; chunk (64) smaller than the page
+    (1, 32, 8, 128, 256, 16, [4096], 0),         # the C4 head layout
+])
+def test_decode_paged_matches_oracle_and_dense_kernel(dtype, B, Hq, Hkv, D, page, blocks, lens, splits):
+    """Paged cache (scope row f1): against the oracle over the gathered cache, and bit for bit against the dense
+    kernel with the same split count (the page table changes addresses, never arithmetic)."""
+    import starflashattention_b200 as sfa
+    q = _rand((B, Hq, D), dtype, 31)
+    k_pool, v_pool, table = _paged_case(dtype, B, Hkv, D, page, blocks, 32)
+    seqlens = torch.tensor(lens, dtype=torch.int32)
+    kc, vc = naive.gather_pages(k_pool, table), naive.gather_pages(v_pool, table)
+    o_ref, lse_ref = naive.decode_attention(q, kc, vc, seqlens)
+    o, lse = sfa.decode_paged(q.cuda(), k_pool.cuda(), v_pool.cuda(), table.cuda(), seqlens.cuda(), num_splits=splits)
+    torch.cuda.synchronize()
+    _assert_close(o, o_ref, dtype, "O")
+    fin = torch.isfinite(lse_ref)
+    assert torch.equal(torch.isfinite(lse.cpu()), fin)
+    assert float((lse.cpu()[fin] - lse_ref[fin]).abs().max() if fin.any() else 0.0) <= 1e-3
+    s = splits or sfa.decode_num_splits(B, blocks * page, Hkv)
+    o_d, lse_d = sfa.decode(q.cuda(), kc.cuda(), vc.cuda(), seqlens.cuda(), num_splits=s)
+    o_p, lse_p = sfa.decode_paged(q.cuda(), k_pool.cuda(), v_pool.cuda(), table.cuda(), seqlens.cuda(), num_splits=s)
+    assert torch.equal(o_p, o_d) and torch.equal(lse_p, lse_d)
+
+
+def test_decode_paged_shared_pages_and_strided_table():
+    """Two sequences may name the same pool pages (a shared prefix), and the table may be a view with a row stride."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    q = _rand((2, 8, 128), dtype, 41)
+    k_pool, v_pool, _ = _paged_case(dtype, 2, 2, 128, 64, 8, 42)
+    wide = torch.zeros((2, 12), dtype=torch.int32)
+    wide[0, :8] = torch.tensor([3, 1, 4, 15, 9, 2, 6, 5])
+    wide[1, :8] = torch.tensor([3, 1, 4, 15, 20, 19, 18, 17])      # first four pages shared
+    table = wide[:, :8]                                           # row stride 12
+    seqlens = torch.tensor([500, 301], dtype=torch.int32)
+    o_ref, lse_ref = naive.decode_attention(q, naive.gather_pages(k_pool, table), naive.gather_pages(v_pool, table), seqlens)
+    o, lse = sfa.decode_paged(q.cuda(), k_pool.cuda(), v_pool.cuda(), wide.cuda()[:, :8], seqlens.cuda())
+    _assert_close(o, o_ref, dtype, "O")
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+
+
+def test_decode_paged_rejects_bad_arguments():
+    import starflashattention_b200 as sfa
+    from starflashattention_b200._capi import StarFlashAttentionError
+    q = torch.zeros((1, 4, 128), dtype=torch.float16, device="cuda")
+    sl = torch.tensor([10], dtype=torch.int32, device="cuda")
+    table = torch.zeros((1, 2), dtype=torch.int32, device="cuda")
+    for page in (8, 24):                                          # below 16, not a power of two
+        pool = torch.zeros((4, page, 4, 128), dtype=torch.float16, device="cuda")
+        with pytest.raises(StarFlashAttentionError):
+            sfa.decode_paged(q, pool, pool, table, sl)
+    pool = torch.zeros((4, 16, 4, 128), dtype=torch.float16, device="cuda")
+    with pytest.raises(ValueError):
+        sfa.decode_paged(q, pool, pool, table.to(torch.int64), sl)
+    with pytest.raises(ValueError):
+        sfa.decode_paged(q, pool, pool, table, None)
+
+
+def test_decode_paged_full_c4_shape_equals_dense():
+    """BASELINE config 4 at full size through a shuffled page table (page 256): bit-identical to the dense kernel."""
+    import starflashattention_b200 as sfa
+    dtype, B, Hq, Hkv, D, M, page = torch.bfloat16, 8, 32, 8, 128, 32768, 256
+    g = torch.Generator(device="cuda").manual_seed(5)
+    blocks = M // page
+    k_pool = torch.randn((B * blocks, page, Hkv, D), generator=g, device="cuda", dtype=torch.float32).to(dtype)
+    v_pool = torch.randn((B * blocks, page, Hkv, D), generator=g, device="cuda", dtype=torch.float32).to(dtype)
+    q = torch.randn((B, Hq, D), generator=g, device="cuda", dtype=torch.float32).to(dtype)
+    table = torch.randperm(B * blocks, generator=g, device="cuda").reshape(B, blocks).to(torch.int32)
+    sl = torch.tensor([M, M - 1, M - 255, 16384, 20000, 31111, M, 257], dtype=torch.int32, device="cuda")
+    o_p, lse_p = sfa.decode_paged(q, k_pool, v_pool, table, sl)
+    kc = k_pool[table.long().reshape(-1)].reshape(B, M, Hkv, D)
+    vc = v_pool[table.long().reshape(-1)].reshape(B, M, Hkv, D)
+    o_d, lse_d = sfa.decode(q, kc, vc, sl)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o_p.float()).all() and torch.isfinite(lse_p).all()
+    assert torch.equal(o_p, o_d) and torch.equal(lse_p, lse_d)
+
+
 def test_decode_outlier_score_does_not_overflow():
     import starflashattention_b200 as sfa
     dtype = torch.float16
@@ -370,6 +463,14 @@ def test_torch_extension_fwd_and_decode(torch_ext):
     sl = torch.tensor([1000, 17], dtype=torch.int32)
     o_ref, lse_ref = naive.decode_attention(qd, kc, vc, sl)
     o, lse = torch_ext.decode(qd.cuda(), kc.cuda(), vc.cuda(), sl.cuda())
+    assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 2e-3
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+    # the same cache cut into 8 pages of 128 keys per sequence (1000 -> 1024 rows), pages in reverse order
+    pad = torch.zeros(2, 24, 2, 128, dtype=torch.float16)
+    k_pool = torch.cat([kc, pad], 1).reshape(16, 128, 2, 128).flip(0).contiguous()
+    v_pool = torch.cat([vc, pad], 1).reshape(16, 128, 2, 128).flip(0).contiguous()
+    table = (15 - torch.arange(16)).reshape(2, 8).to(torch.int32)
+    o, lse = torch_ext.decode_paged(qd.cuda(), k_pool.cuda(), v_pool.cuda(), table.cuda(), sl.cuda())
     assert float((o.float().cpu() - o_ref.float()).abs().max()) <= 2e-3
     assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
 

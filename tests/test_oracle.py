@@ -114,3 +114,13 @@ def test_decode_zero_length():
     k = torch.randn(2, 8, 2, 16)
     o, lse = naive.decode_attention(q, k, k, torch.tensor([0, 5]))
     assert torch.all(o[0] == 0) and torch.isinf(lse[0]).all() and torch.isfinite(lse[1]).all()
+
+
+def test_gather_pages_is_the_dense_cache_the_table_names():
+    pool = torch.arange(6 * 4 * 2 * 8, dtype=torch.float32).reshape(6, 4, 2, 8)
+    table = torch.tensor([[5, 0, 2], [1, 1, 3]], dtype=torch.int32)
+    dense = naive.gather_pages(pool, table)
+    assert dense.shape == (2, 12, 2, 8)
+    for b in range(2):
+        for i in range(3):
+            assert torch.equal(dense[b, 4 * i:4 * i + 4], pool[int(table[b, i])])
