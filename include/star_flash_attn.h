@@ -187,6 +187,36 @@ typedef struct sfa_decoder_step_args {
 
 int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream);
 
+/* ---------------------------------------------------------------- decoder step over a paged cache ---
+ * The same fused step (RoPE of q and k at position seq_len[b], append of k, v at row seq_len[b], attention over
+ * seq_len[b] + 1 keys; intended by src/flash_attn.cu:591-601,696-701) with GQA and with the cache held as page
+ * pools (num_pages, page_size, heads_kv, head_dim) behind a block table (see sfa_decode_paged).  The page of row
+ * seq_len[b], block_table[b][seq_len[b] / page_size], must already be assigned by the caller; a sequence with
+ * seq_len[b] >= max_len appends nothing and attends over its max_len cached keys.
+ * qkv: per token (heads_q + 2 * heads_kv, head_dim) - the q heads, then the k heads, then the v heads - with row
+ * stride `qkv_stride` elements.  rotary tables (max_len, rotary_dim / 2) in the data dtype, or both NULL. */
+typedef struct sfa_decoder_step_paged_args {
+    const void* qkv;
+    void* o;           /* (batch, heads_q, head_dim) contiguous */
+    float* lse;        /* optional (batch, heads_q) */
+    const int32_t* seq_len;
+    void* k_pool;
+    void* v_pool;
+    const int32_t* block_table;
+    const void* rotary_cos_table;
+    const void* rotary_sin_table;
+    int64_t page_stride, row_stride, head_stride; /* of both pools, in elements */
+    int64_t block_table_stride;
+    int64_t qkv_stride;
+    int32_t batch_size, max_len, heads_q, heads_kv, head_dim, page_size, num_pages;
+    int32_t rotary_embedding_dim;
+    float softmax_scale; /* <= 0: 1 / sqrt(head_dim) */
+    int32_t num_splits;  /* <= 0: launcher's choice */
+    int32_t dtype;
+} sfa_decoder_step_paged_args;
+
+int sfa_decoder_step_paged(const sfa_decoder_step_paged_args* args, void* stream);
+
 /* cos/sin tables (max_seq_len, rot_dim/2): angle = pos / 10000^(2i/rot_dim). */
 int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int32_t rot_dim,
                      int32_t dtype, void* stream);

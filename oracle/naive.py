@@ -180,6 +180,34 @@ def decode_step_reference(qkv: torch.Tensor, k_cache_table: torch.Tensor,
     return torch.stack(outs), torch.stack(lses), torch.stack(kn), torch.stack(vn)
 
 
+def decode_step_gqa(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                    seq_len: torch.Tensor, rotary_dim: Optional[int] = None, table_dtype: Optional[torch.dtype] = None,
+                    softmax_scale: Optional[float] = None):
+    """The decoder step of decode_step_reference for grouped query heads and one dense cache per call:
+    q (B,Hq,D), k / v (B,Hkv,D) of the new token, caches (B,M,Hkv,D), seq_len (B,) tokens already cached.
+    Same order of operations (RoPE at position seq_len[b] in fp32 and cast back, append at row seq_len[b],
+    attention over seq_len[b] + 1 keys; src/flash_attn.cu:591-601,696-701, testFlashDecoder.py:61-94).
+    Returns (O (B,Hq,D), LSE (B,Hq), rotated k (B,Hkv,D)); the caches are not mutated."""
+    B, Hq, D = q.shape
+    rd = D if rotary_dim is None else rotary_dim
+    outs, lses, kn = [], [], []
+    for b in range(B):
+        pos = int(seq_len[b])
+        cos, sin = rope_cos_sin(pos, rd)
+        if table_dtype is not None:
+            cos, sin = cos.to(table_dtype), sin.to(table_dtype)
+        qb, kb = q[b].clone(), k[b].clone()
+        qb[:, :rd] = apply_rope(qb[:, :rd], cos, sin)
+        kb[:, :rd] = apply_rope(kb[:, :rd], cos, sin)
+        keys = torch.cat([k_cache[b, :pos], kb[None]], dim=0)
+        vals = torch.cat([v_cache[b, :pos], v[b][None]], dim=0)
+        o, l = attention_fwd(qb[None, None], keys[None], vals[None], softmax_scale=softmax_scale)
+        outs.append(o[0, 0])
+        lses.append(l[0, :, 0])
+        kn.append(kb)
+    return torch.stack(outs), torch.stack(lses), torch.stack(kn)
+
+
 def combine_splits(o_part: torch.Tensor, m_part: torch.Tensor, l_part: torch.Tensor):
     """Merge split-KV partials (intended form of flash_combine_kernel, src/flash_attn.cu:877-935).
 

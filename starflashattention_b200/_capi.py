@@ -16,7 +16,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step",
+    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -65,6 +65,20 @@ class DecodePagedArgs(C.Structure):
     ]
 
 
+class DecoderStepPagedArgs(C.Structure):
+    _fields_ = [
+        ("qkv", C.c_void_p), ("o", C.c_void_p), ("lse", C.c_void_p), ("seq_len", C.c_void_p),
+        ("k_pool", C.c_void_p), ("v_pool", C.c_void_p), ("block_table", C.c_void_p),
+        ("rotary_cos_table", C.c_void_p), ("rotary_sin_table", C.c_void_p),
+        ("page_stride", C.c_int64), ("row_stride", C.c_int64), ("head_stride", C.c_int64),
+        ("block_table_stride", C.c_int64), ("qkv_stride", C.c_int64),
+        ("batch_size", C.c_int32), ("max_len", C.c_int32), ("heads_q", C.c_int32), ("heads_kv", C.c_int32),
+        ("head_dim", C.c_int32), ("page_size", C.c_int32), ("num_pages", C.c_int32),
+        ("rotary_embedding_dim", C.c_int32), ("softmax_scale", C.c_float), ("num_splits", C.c_int32),
+        ("dtype", C.c_int32),
+    ]
+
+
 class DecoderStepArgs(C.Structure):
     _fields_ = [
         ("qkv", C.c_void_p), ("o", C.c_void_p), ("seq_len", C.c_void_p),
@@ -108,6 +122,8 @@ def _load() -> C.CDLL:
     lib.sfa_decode_workspace_bytes.restype = C.c_size_t
     lib.sfa_decoder_step.argtypes = [C.POINTER(DecoderStepArgs), C.c_void_p]
     lib.sfa_decoder_step.restype = C.c_int
+    lib.sfa_decoder_step_paged.argtypes = [C.POINTER(DecoderStepPagedArgs), C.c_void_p]
+    lib.sfa_decoder_step_paged.restype = C.c_int
     lib.sfa_rotary_table.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     lib.sfa_rotary_table.restype = C.c_int
     lib.sfa_fill.argtypes = [C.c_void_p, C.c_float, C.c_int64, C.c_int32, C.c_void_p]

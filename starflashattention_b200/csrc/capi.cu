@@ -149,6 +149,39 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     return decode_impl(d, /*seqlen_add=*/1, stream, &f);
 }
 
+int decoder_step_paged_impl(const sfa_decoder_step_paged_args& a, cudaStream_t stream) {
+    int rc = check_dtype(a.dtype);
+    if (rc) return rc;
+    if (!a.qkv || !a.o || !a.seq_len || !a.k_pool || !a.v_pool || !a.block_table)
+        return fail(SFA_ERR_INVALID, "paged decoder step: null tensor pointer");
+    if (a.batch_size < 0 || a.max_len <= 0 || a.heads_q <= 0 || a.heads_kv <= 0 || a.num_pages <= 0)
+        return fail(SFA_ERR_INVALID, "paged decoder step: bad dimension");
+    if (a.page_size < 16 || (a.page_size & (a.page_size - 1)))
+        return fail(SFA_ERR_INVALID, "paged decoder step: page_size must be a power of two >= 16");
+    if (a.block_table_stride < ((int64_t)a.max_len + a.page_size - 1) / a.page_size)
+        return fail(SFA_ERR_INVALID, "paged decoder step: block table rows are shorter than max_len / page_size");
+    if (a.qkv_stride < (int64_t)(a.heads_q + 2 * a.heads_kv) * a.head_dim || a.qkv_stride % 8)
+        return fail(SFA_ERR_INVALID, "paged decoder step: qkv stride must be >= (heads_q + 2 heads_kv)*head_dim and a multiple of 8");
+    if ((uintptr_t)a.qkv % 16) return fail(SFA_ERR_INVALID, "paged decoder step: qkv must be 16-byte aligned");
+    if (a.rotary_embedding_dim % 2 || a.rotary_embedding_dim > a.head_dim || a.rotary_embedding_dim < 0)
+        return fail(SFA_ERR_INVALID, "rotary_embedding_dim must be even and <= head_dim");
+    if ((a.rotary_cos_table == nullptr) != (a.rotary_sin_table == nullptr))
+        return fail(SFA_ERR_INVALID, "rotary cos and sin tables must be given together");
+    sfa_decode_args d = {};
+    d.q = nullptr; d.k_cache = a.k_pool; d.v_cache = a.v_pool;
+    d.seqlens = a.seq_len; d.o = a.o; d.lse = a.lse;
+    d.batch = a.batch_size; d.seqlen_k = a.max_len - 1; d.heads_q = a.heads_q; d.heads_kv = a.heads_kv; d.head_dim = a.head_dim;
+    d.q_batch_stride = (int64_t)a.heads_q * a.head_dim; d.q_head_stride = a.head_dim;
+    d.k_batch_stride = a.page_stride; d.k_row_stride = a.row_stride; d.k_head_stride = a.head_stride;
+    d.v_batch_stride = a.page_stride; d.v_row_stride = a.row_stride; d.v_head_stride = a.head_stride;
+    d.o_batch_stride = (int64_t)a.heads_q * a.head_dim; d.o_head_stride = a.head_dim;
+    d.softmax_scale = a.softmax_scale;
+    d.num_splits = a.num_splits; d.dtype = a.dtype;
+    const FusedStep f = {a.qkv, a.rotary_cos_table, a.rotary_sin_table, a.qkv_stride, a.rotary_embedding_dim};
+    const PagedKV pk = {a.block_table, a.block_table_stride, a.page_size};
+    return decode_impl(d, /*seqlen_add=*/1, stream, &f, &pk);
+}
+
 // Local split-KV pass of the sharded decode: always leaves (o_part, ml_part) in the workspace; fills the
 // exchange launch for this rank.
 int shard_local_pass(const sfa_decode_args& a, int rank, int world, ShardLaunch& S, cudaStream_t stream) {
@@ -268,6 +301,11 @@ size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_d
 int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decoder_step: null args");
     return sfa::decoder_step_impl(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decoder_step_paged(const sfa_decoder_step_paged_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decoder_step_paged: null args");
+    return sfa::decoder_step_paged_impl(*args, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sfa_decode_sharded(const sfa_decode_args* local_args, const sfa_shard_comm* comm, void* stream) {

@@ -18,7 +18,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _capi
-from ._capi import DecodeArgs, DecodePagedArgs, DecoderStepArgs, FwdArgs, check, lib
+from ._capi import DecodeArgs, DecodePagedArgs, DecoderStepArgs, DecoderStepPagedArgs, FwdArgs, check, lib
 
 __all__ = ["DecoderStepGraph", "fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
            "launch_count", "decode_num_splits"]
@@ -229,6 +229,58 @@ def mha_fwd_cuda(qkv: torch.Tensor, q_bias, k_bias, v_bias, k_cache_table: torch
     a.dtype = _dtype_code(qkv)
     with torch.cuda.device(dev):
         check(lib.sfa_decoder_step(a, _stream()))
+    return o
+
+
+def decoder_step_paged(qkv: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor,
+                       seq_len: torch.Tensor, heads_q: int, o: Optional[torch.Tensor] = None, *,
+                       rotary_embedding_dim: Optional[int] = None, rotary_cos_table: Optional[torch.Tensor] = None,
+                       rotary_sin_table: Optional[torch.Tensor] = None, lse: Optional[torch.Tensor] = None,
+                       softmax_scale: Optional[float] = None, num_splits: int = 0) -> torch.Tensor:
+    """The decoder step of :func:`mha_fwd_cuda` over a PAGED cache, with GQA: RoPE(q, k) at position seq_len[b],
+    append k, v to row seq_len[b] of the sequence (page ``block_table[b, seq_len[b] // page_size]``, assigned by the
+    caller), attend over seq_len[b] + 1 keys - one fused kernel plus the split merge.
+    qkv (B, heads_q + 2 heads_kv, D): q heads, k heads, v heads of the new token; pools (pages, page_size, Hkv, D);
+    block_table int32 (B, blocks); seq_len int32 (B).  Returns o (B, heads_q, D)."""
+    dev = _require_cuda(qkv, k_pool, v_pool, block_table, seq_len, o, rotary_cos_table, rotary_sin_table, lse)
+    if k_pool.dim() != 4 or v_pool.shape != k_pool.shape or k_pool.stride() != v_pool.stride() or k_pool.stride(-1) != 1:
+        raise ValueError("pools must be (pages, page_size, heads_kv, head_dim) with equal strides and a contiguous head_dim")
+    pages, page, Hkv, D = k_pool.shape
+    B = qkv.shape[0]
+    if tuple(qkv.shape) != (B, heads_q + 2 * Hkv, D) or qkv.stride(-1) != 1 or qkv.stride(1) != D:
+        raise ValueError("qkv must be (batch, heads_q + 2 * heads_kv, head_dim) with a dense token row")
+    if not (qkv.dtype == k_pool.dtype == v_pool.dtype):
+        raise TypeError("qkv and the pools must share one dtype")
+    if block_table.dtype != torch.int32 or block_table.dim() != 2 or block_table.shape[0] != B or block_table.stride(1) != 1:
+        raise ValueError("block_table must be int32 (batch, blocks) with contiguous rows")
+    if seq_len.dtype != torch.int32 or not seq_len.is_contiguous() or seq_len.numel() != B:
+        raise ValueError("seq_len must be a contiguous int32 tensor of shape (batch,)")
+    if o is None:
+        o = torch.empty((B, heads_q, D), dtype=qkv.dtype, device=dev)
+    elif tuple(o.shape) != (B, heads_q, D) or o.dtype != qkv.dtype or not o.is_contiguous():
+        raise ValueError("o must be a contiguous (batch, heads_q, head_dim) tensor of the data dtype")
+    max_len = block_table.shape[1] * page
+    rd = D if rotary_embedding_dim is None else rotary_embedding_dim
+    for t in (rotary_cos_table, rotary_sin_table):
+        if t is not None and (t.dtype != qkv.dtype or not t.is_contiguous() or t.dim() != 2 or
+                              t.shape[0] < max_len or t.shape[1] != rd // 2):
+            raise ValueError("rotary tables must be contiguous (>= blocks * page_size, rotary_embedding_dim/2) in the data dtype")
+    a = DecoderStepPagedArgs()
+    a.qkv, a.o, a.seq_len = qkv.data_ptr(), o.data_ptr(), seq_len.data_ptr()
+    a.lse = lse.data_ptr() if lse is not None else None
+    a.k_pool, a.v_pool, a.block_table = k_pool.data_ptr(), v_pool.data_ptr(), block_table.data_ptr()
+    a.rotary_cos_table = rotary_cos_table.data_ptr() if rotary_cos_table is not None else None
+    a.rotary_sin_table = rotary_sin_table.data_ptr() if rotary_sin_table is not None else None
+    a.page_stride, a.row_stride, a.head_stride = k_pool.stride(0), k_pool.stride(1), k_pool.stride(2)
+    a.block_table_stride, a.qkv_stride = block_table.stride(0), qkv.stride(0)
+    a.batch_size, a.max_len, a.heads_q, a.heads_kv, a.head_dim = B, max_len, heads_q, Hkv, D
+    a.page_size, a.num_pages = page, pages
+    a.rotary_embedding_dim = rd
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
+    a.num_splits = int(num_splits)
+    a.dtype = _dtype_code(qkv)
+    with torch.cuda.device(dev):
+        check(lib.sfa_decoder_step_paged(a, _stream()))
     return o
 
 

@@ -197,6 +197,80 @@ def test_decode_paged_full_c4_shape_equals_dense():
     assert torch.equal(o_p, o_d) and torch.equal(lse_p, lse_d)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("Hq,Hkv,D,page,use_tables", [(8, 2, 128, 64, True), (4, 4, 128, 16, False), (8, 1, 64, 128, True)])
+def test_decoder_step_paged_matches_oracle_and_appends_into_the_page(dtype, Hq, Hkv, D, page, use_tables):
+    """Fused RoPE + append + attention over a paged cache with GQA: positions at a page start, a page end, mid-page
+    and on an empty sequence; the appended rows land in the page the block table names and nothing else changes."""
+    import starflashattention_b200 as sfa
+    B, blocks = 4, 6
+    max_len = blocks * page
+    k_pool, v_pool, table = _paged_case(dtype, B, Hkv, D, page, blocks, 51)
+    qkv = _rand((B, Hq + 2 * Hkv, D), dtype, 55)
+    seq = torch.tensor([2 * page, 3 * page - 1, page + 7, 0], dtype=torch.int32)
+    kc, vc = naive.gather_pages(k_pool, table), naive.gather_pages(v_pool, table)
+    q, k, v = qkv[:, :Hq], qkv[:, Hq:Hq + Hkv], qkv[:, Hq + Hkv:]
+    o_ref, lse_ref, k_rot = naive.decode_step_gqa(q, k, v, kc, vc, seq, table_dtype=dtype if use_tables else None)
+    cos = sin = None
+    if use_tables:
+        cos, sin = sfa.compute_rotary_table(max_len, D, dtype=dtype)
+    kp, vp = k_pool.cuda(), v_pool.cuda()
+    lse = torch.empty((B, Hq), dtype=torch.float32, device="cuda")
+    o = sfa.decoder_step_paged(qkv.cuda(), kp, vp, table.cuda(), seq.cuda(), Hq, rotary_cos_table=cos,
+                               rotary_sin_table=sin, lse=lse, num_splits=3)
+    torch.cuda.synchronize()
+    _assert_close(o, o_ref, dtype, "O")
+    assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
+    k_want, v_want = k_pool.clone(), v_pool.clone()
+    for b in range(B):
+        pos = int(seq[b])
+        pg, row = int(table[b, pos // page]), pos % page
+        got_k = kp[pg, row].cpu()
+        assert float((got_k.float() - k_rot[b].float()).abs().max()) <= 1e-2
+        k_want[pg, row] = got_k
+        v_want[pg, row] = v[b]
+    assert torch.equal(kp.cpu(), k_want) and torch.equal(vp.cpu(), v_want)
+    # the next token attends over the row just appended: the dense decode over the gathered, updated cache agrees
+    q2 = _rand((B, Hq, D), dtype, 56).cuda()
+    o_p, lse_p = sfa.decode_paged(q2, kp, vp, table.cuda(), (seq + 1).cuda(), num_splits=2)
+    o_d, lse_d = sfa.decode(q2, naive.gather_pages(kp.cpu(), table).cuda(), naive.gather_pages(vp.cpu(), table).cuda(),
+                            (seq + 1).cuda(), num_splits=2)
+    assert torch.equal(o_p, o_d) and torch.equal(lse_p, lse_d)
+
+
+def test_decoder_step_paged_equals_dense_drop_in_step():
+    """MHA, one layer: the paged fused step and `mha_fwd_cuda` over the gathered dense cache give the same bits."""
+    import starflashattention_b200 as sfa
+    dtype, B, H, D, page, blocks = torch.float16, 2, 4, 128, 64, 8
+    M = page * blocks
+    k_pool, v_pool, table = _paged_case(dtype, B, H, D, page, blocks, 61)
+    qkv = _rand((B, 3, H, D), dtype, 65)
+    seq = torch.tensor([300, 511], dtype=torch.int32)
+    kc = naive.gather_pages(k_pool, table)[:, None].contiguous().cuda()      # (B, L=1, M, H, D)
+    vc = naive.gather_pages(v_pool, table)[:, None].contiguous().cuda()
+    o_d = torch.empty((B, H, D), dtype=dtype, device="cuda")
+    sfa.mha_fwd_cuda(qkv.cuda(), None, None, None, kc, vc, seq.cuda(), o_d, B, M, H, D, D, M, 1, 0, num_splits=4)
+    kp, vp = k_pool.cuda(), v_pool.cuda()
+    o_p = sfa.decoder_step_paged(qkv.reshape(B, 3 * H, D).cuda(), kp, vp, table.cuda(), seq.cuda(), H, num_splits=4)
+    torch.cuda.synchronize()
+    assert torch.equal(o_p, o_d)
+    assert torch.equal(naive.gather_pages(kp.cpu(), table), kc[:, 0].cpu())
+    assert torch.equal(naive.gather_pages(vp.cpu(), table), vc[:, 0].cpu())
+
+
+def test_decoder_step_paged_full_cache_does_not_append():
+    import starflashattention_b200 as sfa
+    dtype, B, Hq, Hkv, D, page, blocks = torch.bfloat16, 1, 8, 2, 128, 32, 4
+    k_pool, v_pool, table = _paged_case(dtype, B, Hkv, D, page, blocks, 71)
+    qkv = _rand((B, Hq + 2 * Hkv, D), dtype, 75)
+    seq = torch.tensor([page * blocks], dtype=torch.int32)                   # no room for the new token
+    kp, vp = k_pool.cuda(), v_pool.cuda()
+    o = sfa.decoder_step_paged(qkv.cuda(), kp, vp, table.cuda(), seq.cuda(), Hq)
+    torch.cuda.synchronize()
+    assert torch.equal(kp.cpu(), k_pool) and torch.equal(vp.cpu(), v_pool)
+    assert bool(torch.isfinite(o.float()).all())
+
+
 def test_decode_outlier_score_does_not_overflow():
     import starflashattention_b200 as sfa
     dtype = torch.float16
