@@ -28,6 +28,7 @@
 #include "merge.cuh"
 #include "rope.cuh"
 
+#include <cooperative_groups.h>
 #include <math.h>
 #include <type_traits>
 
@@ -122,6 +123,7 @@ struct MergeSmem {
     float o[kWarps][8][D];
     float m[kWarps][8];
     float l[kWarps][8];
+    float M[8], L[8];   // CLUSTER: the CTA's merged (m, l) per head, read by the other CTAs of the cluster
 };
 
 __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {   // transpose of an 8x8 b16 matrix held one row-pair per thread
@@ -136,7 +138,11 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {   // transpose
 // PAGED: the cache is a pool of pages found through a per-sequence block table.  A 16-key step never straddles a
 // page (page_size is a power of two >= 16 and chunks start on multiples of 64), so the indirection is one
 // warp-uniform table read per step; everything after the row pointer is the same streaming code.
-template <typename T, int D, bool FUSED, bool SWAP, bool PAGED = false>
+// CLUSTER: the num_splits (2 .. 8) CTAs of one (batch, kv-head) form a thread-block cluster and merge their
+// partials through distributed shared memory - no partials in global memory and no combine launch.  The combine
+// kernel costs ~5 us on its own, a sixth of a decoder step over a few thousand keys and half of one over a few
+// hundred (the reference's own example shapes).
+template <typename T, int D, bool FUSED, bool SWAP, bool PAGED = false, bool CLUSTER = false>
 __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kernel(const DecodeParams p) {
     constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
     constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
@@ -405,7 +411,10 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
             acc += sc * sm.o[w][hh][d];
         }
         const int hq = hk * g + hh;
-        if (p.num_splits == 1 && !p.force_partials) {
+        if constexpr (CLUSTER) {
+            sm.o[0][hh][d] = acc;   // this thread alone reads and writes column (hh, d)
+            if (d == 0) { sm.M[hh] = M; sm.L[hh] = L; }
+        } else if (p.num_splits == 1 && !p.force_partials) {
             const float inv = L > 0.f ? 1.f / L : 0.f;
             T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
             orow[d] = (T)(acc * inv);
@@ -415,6 +424,38 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
             p.o_part[row * D + d] = acc;
             if (d == 0) p.ml_part[row] = make_float2(M, L);
         }
+    }
+    if constexpr (CLUSTER) {
+        // The splits of this (batch, kv-head) are the CTAs of the cluster (rank = split).  Every CTA merges a
+        // 128-column slice of the group's g x D outputs out of all the CTAs' shared memory.
+        namespace cg = cooperative_groups;
+        cg::cluster_group cluster = cg::this_cluster();
+        cluster.sync();
+        const int S = p.num_splits, rank = (int)cluster.block_rank();
+        for (int idx = rank * (kWarps * 32) + threadIdx.x; idx < g * D; idx += S * (kWarps * 32)) {
+            const int hh = idx / D, d = idx - hh * D;
+            float ms[8], M = -INFINITY;
+#pragma unroll
+            for (int s2 = 0; s2 < 8; ++s2) {
+                ms[s2] = s2 < S ? *cluster.map_shared_rank(&sm.M[hh], s2) : -INFINITY;
+                M = fmaxf(M, ms[s2]);
+            }
+            float L = 0.f, acc = 0.f;
+#pragma unroll
+            for (int s2 = 0; s2 < 8; ++s2) {
+                if (s2 < S) {
+                    const float w = (ms[s2] == -INFINITY) ? 0.f : exp2f(ms[s2] - M);
+                    L += w * *cluster.map_shared_rank(&sm.L[hh], s2);
+                    acc += w * *cluster.map_shared_rank(&sm.o[0][hh][d], s2);
+                }
+            }
+            const int hq = hk * g + hh;
+            const float inv = L > 0.f ? 1.f / L : 0.f;
+            T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
+            orow[d] = (T)(acc * inv);
+            if (d == 0 && p.lse) p.lse[(int64_t)b * p.heads_q + hq] = L > 0.f ? (M + log2f(L)) * kLn2 : -INFINITY;
+        }
+        cluster.sync();   // nobody leaves while its shared memory is still being read
     }
 }
 
@@ -435,9 +476,38 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
     }
 }
 
+constexpr int kMaxClusterSplits = 8;   // portable cluster size
+
+// In-cluster merge (see the CLUSTER note above the kernel): SFA_DECODE_CLUSTER=0 keeps the two-launch form.
+inline bool decode_cluster_enabled() {
+    const char* e = getenv("SFA_DECODE_CLUSTER");
+    return e ? atoi(e) != 0 : true;
+}
+
+template <typename T, int D, bool FUSED, bool PAGED>
+int launch_cluster(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.num_splits, a.heads_kv, a.batch);
+    cfg.blockDim = dim3(kWarps * 32);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = a.num_splits; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    SFA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, decode_splitkv_kernel<T, D, FUSED, true, PAGED, true>, p));
+    count_launch();
+    return SFA_OK;
+}
+
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
     dim3 grid(a.num_splits, a.heads_kv, a.batch);
+    if (a.num_splits >= 2 && a.num_splits <= kMaxClusterSplits && !a.force_partials && decode_cluster_enabled() &&
+        (a.block_table || decode_swap_enabled())) {
+        if (a.block_table) return a.fused_qkv ? launch_cluster<T, D, true, true>(a, p, stream) : launch_cluster<T, D, false, true>(a, p, stream);
+        return a.fused_qkv ? launch_cluster<T, D, true, false>(a, p, stream) : launch_cluster<T, D, false, false>(a, p, stream);
+    }
     if (a.block_table) {
         if (a.fused_qkv) decode_splitkv_kernel<T, D, true, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
         else decode_splitkv_kernel<T, D, false, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
@@ -461,8 +531,12 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
 
 }  // namespace
 
-// Splits heuristic: fill every SM with `waves` rounds of resident CTAs (3 per SM, see the launch
-// bounds), never cutting a sequence into chunks shorter than 256 keys.
+// Splits heuristic.  (1) When 2 .. 8 splits per (batch, kv-head) unit fill ONE wave of resident CTAs (4 per SM), take
+// that: the splits of a unit then form a thread-block cluster that merges in shared memory (one launch, no
+// tail wave).  Measured (tools/decode_split_sweep.py, profiles/r1g_split_sweep.txt): 64 units x 8 splits beat the
+// older 16 .. 28 splits + combine launch by 8 - 16 % from 4k to 32k keys; 256 units x 2 by 24 %.  (2) Few units and
+// a short cache (launch-latency bound): up to 8 cluster splits of at least 128 keys.  (3) Otherwise (few units, long
+// cache) the two-launch form: `waves` rounds of 3 CTAs per SM, chunks of at least 256 keys, at most 256 splits.
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
     static int waves = [] {
         const char* e = getenv("SFA_DECODE_WAVES");
@@ -478,6 +552,17 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
     if (s > max_by_len) s = max_by_len;
     if (s > 256) s = 256;   // one long sequence (batch 1): 8 kv-heads x 222 chunks fill 4 waves of 3 CTAs/SM
     if (s < 1) s = 1;
+    if (decode_cluster_enabled() && decode_swap_enabled()) {
+        const long one_wave = (long)sm_count * 4 / units;   // splits per unit that fill the resident CTA slots once
+        if (one_wave >= 2) {
+            long sc = one_wave < kMaxClusterSplits ? one_wave : kMaxClusterSplits;
+            const long by_len = max_seqlen / 128 > 0 ? max_seqlen / 128 : 1;
+            if (sc > by_len) sc = by_len;
+            // 8 splits still count as the one-wave choice while they fill 80 % of the slots (64 units: 512 of 592)
+            if (one_wave <= kMaxClusterSplits + 2) return (int)sc;
+            if (s <= kMaxClusterSplits) return (int)(s > sc ? s : sc);
+        }
+    }
     return (int)s;
 }
 

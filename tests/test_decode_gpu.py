@@ -271,6 +271,42 @@ def test_decoder_step_paged_full_cache_does_not_append():
     assert bool(torch.isfinite(o.float()).all())
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("B,Hq,Hkv,D,M,lens", [
+    (2, 8, 2, 128, 3000, [3000, 1777]),
+    (3, 8, 1, 64, 700, [1, 64, 700]),            # splits without keys take part in the cluster merge with weight 0
+    (2, 4, 4, 128, 512, [0, 512]),               # an empty sequence: O = 0, LSE = -inf
+])
+def test_decode_cluster_merge_matches_two_launch_form(dtype, B, Hq, Hkv, D, M, lens, monkeypatch):
+    """2 .. 8 splits merge inside a thread-block cluster through distributed shared memory (one launch); the
+    two-launch form (partials in global memory + combine kernel, SFA_DECODE_CLUSTER=0) is the same arithmetic up
+    to the order of the fp32 sums.  Both against the oracle."""
+    import starflashattention_b200 as sfa
+    q, kc, vc = _rand((B, Hq, D), dtype, 91), _rand((B, M, Hkv, D), dtype, 92), _rand((B, M, Hkv, D), dtype, 93)
+    sl = torch.tensor(lens, dtype=torch.int32)
+    o_ref, lse_ref = naive.decode_attention(q, kc, vc, sl)
+    fin = torch.isfinite(lse_ref)
+    qd, kd, vd, sd = q.cuda(), kc.cuda(), vc.cuda(), sl.cuda()
+    for s in (2, 3, 5, 8):
+        res = {}
+        for cl in ("1", "0"):
+            monkeypatch.setenv("SFA_DECODE_CLUSTER", cl)
+            n0 = sfa.launch_count()
+            o, lse = sfa.decode(qd, kd, vd, sd, num_splits=s)
+            torch.cuda.synchronize()
+            res[cl] = (o.float().cpu(), lse.cpu(), sfa.launch_count() - n0)
+        assert res["1"][2] == 1 and res["0"][2] == 2
+        _assert_close(res["1"][0], o_ref, dtype, f"O, {s} cluster splits")
+        assert torch.equal(torch.isfinite(res["1"][1]), fin)
+        assert float((res["1"][1][fin] - lse_ref[fin]).abs().max()) <= 1e-3
+        assert float((res["1"][0] - res["0"][0]).abs().max()) <= 1e-3
+        assert float((res["1"][1][fin] - res["0"][1][fin]).abs().max()) <= 1e-5
+    monkeypatch.setenv("SFA_DECODE_CLUSTER", "1")
+    n0 = sfa.launch_count()
+    sfa.decode(qd, kd, vd, sd, num_splits=9)      # more than a portable cluster: two launches
+    assert sfa.launch_count() - n0 == 2
+
+
 def test_decode_outlier_score_does_not_overflow():
     import starflashattention_b200 as sfa
     dtype = torch.float16
@@ -411,7 +447,8 @@ def test_decoder_step_fused_equals_three_launch_form(dtype, D, monkeypatch):
         torch.cuda.synchronize()
         outs.append((o.cpu(), lse.cpu(), kc_d.cpu(), vc_d.cpu(), sfa.launch_count() - n0))
     (o1, l1, k1, v1, n1), (o0, l0, k0, v0, n0_) = outs
-    assert n1 == 2 and n0_ == 3            # fused: split-KV + combine; unfused: RoPE/append + split-KV + combine
+    # fused: one split-KV launch whose 4 splits merge in their cluster; unfused: RoPE/append kernel first
+    assert n1 == 1 and n0_ == 2
     assert torch.equal(k1, k0) and torch.equal(v1, v0)
     assert torch.equal(o1, o0) and torch.equal(l1, l0)
 
