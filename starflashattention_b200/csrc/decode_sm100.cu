@@ -476,7 +476,11 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
     }
 }
 
-constexpr int kMaxClusterSplits = 8;   // portable cluster size
+// Portable cluster size.  Non-portable sizes (9 .. 16, cudaFuncAttributeNonPortableClusterSizeAllowed) were measured
+// and rejected: with the machine full the scheduler cannot pack them (C4: 9 cluster splits 257 us against 179 us for
+// 9 two-launch splits, 16: 232 against 181), and with few units they are erratic (B=4, 4096 keys: 12 splits 25.5 us,
+// 16 splits 35.8 us); profiles/r1g_split_sweep16.txt.
+constexpr int kMaxClusterSplits = 8;
 
 // In-cluster merge (see the CLUSTER note above the kernel): SFA_DECODE_CLUSTER=0 keeps the two-launch form.
 inline bool decode_cluster_enabled() {

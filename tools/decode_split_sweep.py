@@ -16,7 +16,7 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."
 import starflashattention_b200 as sfa  # noqa: E402
 
 SHAPES = [  # B, Hq, Hkv, M
-    (1, 32, 32, 512), (2, 32, 32, 4096), (2, 32, 32, 8192), (1, 32, 8, 4096), (8, 32, 8, 4096),
+    (1, 32, 32, 512), (2, 32, 32, 4096), (2, 32, 32, 8192), (1, 32, 8, 4096), (8, 32, 8, 4096), (4, 32, 8, 4096), (4, 32, 8, 16384),
     (32, 32, 8, 2048), (1, 32, 8, 32768), (4, 32, 8, 32768), (8, 32, 8, 32768),
 ]
 
@@ -49,7 +49,7 @@ def main():
         row = {"auto_splits": auto, "floor_us": nbytes / 6556.8e3}
         os.environ["SFA_DECODE_CLUSTER"] = "1"
         row["auto"] = timed(lambda: sfa.decode(q, kc, vc, sl), flush)
-        for s in (1, 2, 4, 6, 8, 12, 16, 24, 32, 48):
+        for s in (1, 2, 4, 6, 8, 9, 10, 12, 14, 16, 18, 24, 32, 48):
             if s * 64 > M and s > 1:
                 continue
             for cl in ("0", "1"):
