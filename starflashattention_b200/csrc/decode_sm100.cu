@@ -540,7 +540,8 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
 // tail wave).  Measured (tools/decode_split_sweep.py, profiles/r1g_split_sweep.txt): 64 units x 8 splits beat the
 // older 16 .. 28 splits + combine launch by 8 - 16 % from 4k to 32k keys; 256 units x 2 by 24 %.  (2) Few units and
 // a short cache (launch-latency bound): up to 8 cluster splits of at least 128 keys.  (3) Otherwise (few units, long
-// cache) the two-launch form: `waves` rounds of 3 CTAs per SM, chunks of at least 256 keys, at most 256 splits.
+// cache) the two-launch form: one wave when that is at most 24 splits, else `waves` rounds of 3 CTAs per SM, chunks
+// of at least 256 keys, at most 256 splits.
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
     static int waves = [] {
         const char* e = getenv("SFA_DECODE_WAVES");
@@ -565,6 +566,9 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
             // 8 splits still count as the one-wave choice while they fill 80 % of the slots (64 units: 512 of 592)
             if (one_wave <= kMaxClusterSplits + 2) return (int)sc;
             if (s <= kMaxClusterSplits) return (int)(s > sc ? s : sc);
+            // one wave is also the best two-launch count while it means at most ~24 splits (32 units: 16 - 18 splits
+            // 58 us at 16k keys and 99 us at 32k, against 62 and 101 us for the 56 of the rule below)
+            if (one_wave <= 24 && s > one_wave) return (int)(one_wave < by_len ? one_wave : by_len);
         }
     }
     return (int)s;
