@@ -362,6 +362,10 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
         if (cta_has_new && warp == ((new_base - k_begin) / kStepKeys) % kWarps) step(new_base, std::true_type{});
     }
 
+    // Two-launch form: the combine kernel may be scheduled from here on (programmatic dependent launch); its
+    // griddepcontrol.wait still holds it until this whole grid has completed and its partials are visible, so
+    // only the launch latency moves under this kernel's tail.
+    if constexpr (!CLUSTER) asm volatile("griddepcontrol.launch_dependents;");
     // ---- merge the four warp states
     if constexpr (SWAP) {
 #pragma unroll
@@ -466,6 +470,7 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
     __shared__ MergeScratch<D> sc;
     const int hq = blockIdx.x, b = blockIdx.y;
     const int64_t row0 = ((int64_t)b * p.heads_q + hq) * p.num_splits;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // the split kernel has completed (no-op without PDL)
     float acc, L, M;
     merge_splits<D>(p.o_part, p.ml_part, row0, p.num_splits, w_sm, sc, acc, L, M);
     if (threadIdx.x < D) {
@@ -526,8 +531,20 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
     count_launch();
     if (a.num_splits > 1 && !a.force_partials) {
         dim3 cgrid(a.heads_q, a.batch);
-        decode_combine_kernel<T, D><<<cgrid, D * kMergeGroups, a.num_splits * sizeof(float), stream>>>(p);
-        SFA_CUDA_CHECK(cudaGetLastError());
+        static const bool pdl = [] { const char* e = getenv("SFA_DECODE_PDL"); return e ? atoi(e) != 0 : true; }();
+        if (pdl) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = cgrid; cfg.blockDim = dim3(D * kMergeGroups);
+            cfg.dynamicSmemBytes = a.num_splits * sizeof(float); cfg.stream = stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            SFA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, decode_combine_kernel<T, D>, p));
+        } else {
+            decode_combine_kernel<T, D><<<cgrid, D * kMergeGroups, a.num_splits * sizeof(float), stream>>>(p);
+            SFA_CUDA_CHECK(cudaGetLastError());
+        }
         count_launch();
     }
     return SFA_OK;
