@@ -147,6 +147,7 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     constexpr int NJ = D / 32;   // 32-wide head_dim blocks of the QK^T contraction (2 MMAs each)
     constexpr int NH = D / 64;   // 64-wide head_dim blocks of the P.V output (8 n-tiles each)
     __shared__ MergeSmem<D> sm;
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // the kernel before this one has completed (no-op without PDL)
 
     const int split = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -362,10 +363,10 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
         if (cta_has_new && warp == ((new_base - k_begin) / kStepKeys) % kWarps) step(new_base, std::true_type{});
     }
 
-    // Two-launch form: the combine kernel may be scheduled from here on (programmatic dependent launch); its
-    // griddepcontrol.wait still holds it until this whole grid has completed and its partials are visible, so
-    // only the launch latency moves under this kernel's tail.
-    if constexpr (!CLUSTER) asm volatile("griddepcontrol.launch_dependents;");
+    // The next kernel on the stream (the combine kernel of the two-launch form, or the next decode call) may be
+    // scheduled from here on (programmatic dependent launch, see decode_pdl_level); its griddepcontrol.wait still
+    // holds it until this whole grid has completed and its writes are visible.
+    asm volatile("griddepcontrol.launch_dependents;");
     // ---- merge the four warp states
     if constexpr (SWAP) {
 #pragma unroll
@@ -471,6 +472,7 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
     const int hq = blockIdx.x, b = blockIdx.y;
     const int64_t row0 = ((int64_t)b * p.heads_q + hq) * p.num_splits;
     asm volatile("griddepcontrol.wait;" ::: "memory");   // the split kernel has completed (no-op without PDL)
+    asm volatile("griddepcontrol.launch_dependents;");    // the next decode kernel may line up behind this one
     float acc, L, M;
     merge_splits<D>(p.o_part, p.ml_part, row0, p.num_splits, w_sm, sc, acc, L, M);
     if (threadIdx.x < D) {
@@ -493,60 +495,67 @@ inline bool decode_cluster_enabled() {
     return e ? atoi(e) != 0 : true;
 }
 
-template <typename T, int D, bool FUSED, bool PAGED>
-int launch_cluster(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
+// Programmatic dependent launch (SFA_DECODE_PDL: 0 off, 1 the combine kernel only, 2 = default every decode kernel):
+// a kernel launched this way may be scheduled once the kernel before it on the stream has executed
+// griddepcontrol.launch_dependents in every CTA (ours do so on leaving the streaming loop; a foreign kernel never does,
+// which means "at completion"), and its own griddepcontrol.wait - the first instruction of both kernels - holds it
+// until that kernel has completed and flushed.  Launch latency and CTA start-up move under the predecessor's tail.
+inline int decode_pdl_level() {
+    static const int level = [] { const char* e = getenv("SFA_DECODE_PDL"); return e ? atoi(e) : 2; }();
+    return level;
+}
+
+template <typename K>
+int launch_ex(K kern, dim3 grid, int threads, size_t smem, int cluster, bool pdl, const DecodeParams& p, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.num_splits, a.heads_kv, a.batch);
-    cfg.blockDim = dim3(kWarps * 32);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = a.num_splits; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
-    SFA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, decode_splitkv_kernel<T, D, FUSED, true, PAGED, true>, p));
+    cfg.gridDim = grid; cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[2];
+    int n = 0;
+    if (cluster > 0) {
+        at[n].id = cudaLaunchAttributeClusterDimension;
+        at[n].val.clusterDim.x = cluster; at[n].val.clusterDim.y = 1; at[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl) {
+        at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = at; cfg.numAttrs = n;
+    SFA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
     count_launch();
     return SFA_OK;
 }
 
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
-    dim3 grid(a.num_splits, a.heads_kv, a.batch);
+    const dim3 grid(a.num_splits, a.heads_kv, a.batch);
+    const int threads = kWarps * 32;
+    const bool pdl_all = decode_pdl_level() >= 2;
     if (a.num_splits >= 2 && a.num_splits <= kMaxClusterSplits && !a.force_partials && decode_cluster_enabled() &&
         (a.block_table || decode_swap_enabled())) {
-        if (a.block_table) return a.fused_qkv ? launch_cluster<T, D, true, true>(a, p, stream) : launch_cluster<T, D, false, true>(a, p, stream);
-        return a.fused_qkv ? launch_cluster<T, D, true, false>(a, p, stream) : launch_cluster<T, D, false, false>(a, p, stream);
+        const int cs = a.num_splits;
+        if (a.block_table)
+            return a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, true, true, true>, grid, threads, 0, cs, pdl_all, p, stream)
+                               : launch_ex(decode_splitkv_kernel<T, D, false, true, true, true>, grid, threads, 0, cs, pdl_all, p, stream);
+        return a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, true, false, true>, grid, threads, 0, cs, pdl_all, p, stream)
+                           : launch_ex(decode_splitkv_kernel<T, D, false, true, false, true>, grid, threads, 0, cs, pdl_all, p, stream);
     }
+    int rc;
     if (a.block_table) {
-        if (a.fused_qkv) decode_splitkv_kernel<T, D, true, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
-        else decode_splitkv_kernel<T, D, false, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
+        rc = a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, true, true>, grid, threads, 0, 0, pdl_all, p, stream)
+                         : launch_ex(decode_splitkv_kernel<T, D, false, true, true>, grid, threads, 0, 0, pdl_all, p, stream);
     } else if (decode_swap_enabled()) {
-        if (a.fused_qkv) decode_splitkv_kernel<T, D, true, true><<<grid, kWarps * 32, 0, stream>>>(p);
-        else decode_splitkv_kernel<T, D, false, true><<<grid, kWarps * 32, 0, stream>>>(p);
+        rc = a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, true>, grid, threads, 0, 0, pdl_all, p, stream)
+                         : launch_ex(decode_splitkv_kernel<T, D, false, true>, grid, threads, 0, 0, pdl_all, p, stream);
     } else {
-        if (a.fused_qkv) decode_splitkv_kernel<T, D, true, false><<<grid, kWarps * 32, 0, stream>>>(p);
-        else decode_splitkv_kernel<T, D, false, false><<<grid, kWarps * 32, 0, stream>>>(p);
+        rc = a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, false>, grid, threads, 0, 0, pdl_all, p, stream)
+                         : launch_ex(decode_splitkv_kernel<T, D, false, false>, grid, threads, 0, 0, pdl_all, p, stream);
     }
-    SFA_CUDA_CHECK(cudaGetLastError());
-    count_launch();
-    if (a.num_splits > 1 && !a.force_partials) {
-        dim3 cgrid(a.heads_q, a.batch);
-        static const bool pdl = [] { const char* e = getenv("SFA_DECODE_PDL"); return e ? atoi(e) != 0 : true; }();
-        if (pdl) {
-            cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = cgrid; cfg.blockDim = dim3(D * kMergeGroups);
-            cfg.dynamicSmemBytes = a.num_splits * sizeof(float); cfg.stream = stream;
-            cudaLaunchAttribute at[1];
-            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-            at[0].val.programmaticStreamSerializationAllowed = 1;
-            cfg.attrs = at; cfg.numAttrs = 1;
-            SFA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, decode_combine_kernel<T, D>, p));
-        } else {
-            decode_combine_kernel<T, D><<<cgrid, D * kMergeGroups, a.num_splits * sizeof(float), stream>>>(p);
-            SFA_CUDA_CHECK(cudaGetLastError());
-        }
-        count_launch();
-    }
+    if (rc) return rc;
+    if (a.num_splits > 1 && !a.force_partials)
+        return launch_ex(decode_combine_kernel<T, D>, dim3(a.heads_q, a.batch), D * kMergeGroups, a.num_splits * sizeof(float), 0,
+                         decode_pdl_level() >= 1, p, stream);
     return SFA_OK;
 }
 
