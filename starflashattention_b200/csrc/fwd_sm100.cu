@@ -55,6 +55,7 @@ struct FwdParams {
     int causal, is_bf16;
     float scale_log2;
     int stagger_cycles;   // head start of warpgroup 0 over warpgroup 1 (see launch_fwd)
+    int load_order;       // 1: prologue loads go out Q0, K0, Q1, V0, ... (default); 0: Q0, Q1, K0, V0, ... (SFA_FWD_LOADORDER)
 };
 
 __device__ int g_fwd_error;
@@ -239,6 +240,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // DBG == 6: prologue / epilogue stamps of CTA (0,0,0): 24 kernel entry, 25 set-up done, 26 last P.V seen by
+    // warpgroup 0, 27 its O rows stored, 28 teardown
+    const bool stamp = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0;
+    if (stamp) g_fwd_probe[24] = clock64();
     // Heavy (late) query blocks first: under the causal mask they own the most key tiles.
     const int m_block = gridDim.x - 1 - blockIdx.x;
     const int h = blockIdx.y, b = blockIdx.z;
@@ -305,23 +310,30 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         fence_barrier_init();
         // The first loads need nobody's consent (the ring starts empty): issue them before the CTA-wide sync so
         // that their latency overlaps the TMEM allocation and the rest of the prologue.
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-            if (n_tiles[q] == 0) continue;
+        // Issue order Q0, K0, then the rest: the first Q.K needs exactly those two tiles (measured on CTA (0,0,0):
+        // 5250 cycles from set-up to the first Q.K issue, all of it waiting for these loads).
+        auto load_q = [&](int q) {
+            if (n_tiles[q] == 0) return;
             mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
 #pragma unroll
             for (int s = 0; s < kSub; ++s)
                 tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
                             64 * s, h, m0 + q * kBlockM, b);
-        }
-        for (int i = 0; i < min(NSTAGE, 2 * n_max); ++i) {
+        };
+        auto load_kv = [&](int i) {
             mbar_arrive_expect_tx(bar_kv_full(i), L::kTileBytes);
             const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
 #pragma unroll
             for (int s = 0; s < kSub; ++s)
                 tma_load_4d(smem_base + L::kRingOff + i * L::kTileBytes + s * L::kSubTileBytes, map, bar_kv_full(i),
                             64 * s, hk, (i >> 1) * kBlockN, b);
-        }
+        };
+        const int n_pre = min(NSTAGE, 2 * n_max);
+        load_q(0);
+        if (p.load_order && n_pre > 0) load_kv(0);
+#pragma unroll
+        for (int q = 1; q < NQ; ++q) load_q(q);
+        for (int i = p.load_order ? 1 : 0; i < n_pre; ++i) load_kv(i);
     }
     if (warp == kSoftmaxWarps + 1) {
         tmem_alloc(smem_base + L::kTmemPtrOff, T::kCols);
@@ -331,6 +343,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    if (stamp) g_fwd_probe[25] = clock64();
 
     // NQ == 2 runs three full warpgroups (the third holds the TMA and MMA warps plus two idle
     // warps) so the register file can be re-split: the softmax warpgroups take what the others give up.
@@ -662,6 +675,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         }
         if (n_q > 0 && ok) ok = wait_barrier(bar_pv_done(q), (n_q - 1) & 1, p.error_flag, 10);
         tc_fence_after();
+        if (stamp) g_fwd_probe[26] = clock64();
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
             uint32_t o[32];
@@ -687,6 +701,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
             p.lse[((int64_t)b * p.heads_q + h) * p.seqlen_q + row] = lse;
         }
+        if (stamp) g_fwd_probe[27] = clock64();
     } else {
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warps of the third warpgroup
     }
@@ -698,6 +713,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         tc_fence_after();
         tmem_dealloc(tmem_base, T::kCols);
     }
+    if (stamp) g_fwd_probe[28] = clock64();
 }
 
 // ------------------------------------------------------------------------------------------ host
@@ -848,6 +864,8 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
     {
         const char* e = getenv("SFA_FWD_STAGGER");
         p.stagger_cycles = e ? atoi(e) : (a.head_dim == 64 ? kStaggerCycles64 : 0);
+        const char* lo = getenv("SFA_FWD_LOADORDER");
+        p.load_order = lo ? atoi(lo) : 1;
     }
     void* flag_addr = nullptr;
     SFA_CUDA_CHECK(cudaGetSymbolAddress(&flag_addr, g_fwd_error));

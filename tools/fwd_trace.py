@@ -45,6 +45,14 @@ def main():
     t0 = ev[0][0]
     for t, name in ev:
         print(f"{t - t0:7d}  {name}")
+    # prologue / epilogue of the CTA (the heaviest query block: 64 key tiles per query tile)
+    t_in, t_setup, t_lastpv, t_stored, t_out = (buf[i] for i in (24, 25, 26, 27, 28))
+    first_qk = buf[32 + 1]                          # q0 j0 "commits flushed, QK issue"
+    first_s = buf[32 + 8]                           # q0 j0 "S seen"
+    if t_in and t_out:
+        print(f"CTA (0,0,0): {t_out - t_in} cycles in all; entry -> set-up done {t_setup - t_in}, -> first QK issue "
+              f"{first_qk - t_in}, -> first S seen {first_s - t_in}; last P.V seen -> O stored {t_stored - t_lastpv}, "
+              f"-> exit {t_out - t_lastpv}")
     # per-tile periods
     for qq in (0, 1):
         ts = [buf[32 + (j * 2 + qq) * 16 + 8] for j in range(8, 60)]
