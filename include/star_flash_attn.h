@@ -224,6 +224,13 @@ int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int3
 int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream);
 
 /* ---------------------------------------------------------------- misc ---------------------- */
+/* Pitched copy between pinned host memory and the device on `stream` (cudaMemcpy2DAsync): `height` rows of
+ * `width_bytes`, row pitches in bytes; kind 1 = host to device, 2 = device to host.  Used by the host-buffer entry
+ * points when a chunk is a slice of heads (rows of a (batch, seqlen, heads, head_dim) tensor are then not contiguous);
+ * the reference's own host path is blocking cudaMemcpy calls (src/flash_attn.cu:973-975). */
+int sfa_copy_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes, size_t height,
+                int32_t kind, void* stream);
+
 const char* sfa_last_error(void);
 int sfa_abi_version(void);
 /* Number of kernels this library has launched in this process (all entry points). */

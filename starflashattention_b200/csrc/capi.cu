@@ -287,6 +287,19 @@ int sfa_decode_paged(const sfa_decode_paged_args* args, void* stream) {
     return sfa::decode_impl(args->base, 0, reinterpret_cast<cudaStream_t>(stream), nullptr, &pk);
 }
 
+int sfa_copy_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes, size_t height,
+                int32_t kind, void* stream) {
+    if (!dst || !src) return sfa::fail(SFA_ERR_INVALID, "sfa_copy_2d: null pointer");
+    if (kind != 1 && kind != 2) return sfa::fail(SFA_ERR_INVALID, "sfa_copy_2d: kind must be 1 (host to device) or 2 (device to host)");
+    if (width_bytes > dst_pitch || width_bytes > src_pitch) return sfa::fail(SFA_ERR_INVALID, "sfa_copy_2d: width exceeds a pitch");
+    if (width_bytes == 0 || height == 0) return SFA_OK;
+    if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
+    SFA_CUDA_CHECK(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, height,
+                                     kind == 1 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost,
+                                     reinterpret_cast<cudaStream_t>(stream)));
+    return SFA_OK;
+}
+
 int sfa_decode_num_splits(const sfa_decode_args* args) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_num_splits: null args");
     const sfa::DeviceInfo* dev = sfa::current_device();

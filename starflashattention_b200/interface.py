@@ -404,6 +404,23 @@ def _pinned(t: torch.Tensor, what: str):
         raise ValueError(f"{what} must live in pinned host memory (tensor.pin_memory())")
 
 
+def _copy_heads(dst: torch.Tensor, src: torch.Tensor, to_device: bool, stream) -> None:
+    """Copy a slice of heads of a (batch, seqlen, heads, head_dim) tensor between pinned host memory and the device
+    as ONE pitched DMA (sfa_copy_2d).  `tensor.copy_` of such a view first gathers it on the host into pageable
+    memory and stalls the pipeline (measured: 4 GB/s against ~50 GB/s).  Both tensors must have uniform row
+    pitches, i.e. (batch, seqlen) must flatten to rows `stride(1)` apart."""
+    def rows(t):
+        if t.stride(3) != 1 or t.stride(2) != t.shape[3] or (t.shape[0] > 1 and t.stride(0) != t.shape[1] * t.stride(1)):
+            raise ValueError("not a pitched (batch, seqlen, heads, head_dim) view")
+        return t.shape[0] * t.shape[1], t.stride(1) * t.element_size(), t.shape[2] * t.shape[3] * t.element_size()
+    n_d, pitch_d, width_d = rows(dst)
+    n_s, pitch_s, width_s = rows(src)
+    if (n_d, width_d) != (n_s, width_s):
+        raise ValueError("shape mismatch in a pitched copy")
+    check(lib.sfa_copy_2d(dst.data_ptr(), pitch_d, src.data_ptr(), pitch_s, width_d, n_d, 1 if to_device else 2,
+                          stream.cuda_stream))
+
+
 def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = False,
              softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
              lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
@@ -452,7 +469,11 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
             with torch.cuda.stream(pipe.s_in):
                 if ev_comp[i & 1] is not None:
                     pipe.s_in.wait_event(ev_comp[i & 1])
-                dq.copy_(src[0], non_blocking=True); dk.copy_(src[1], non_blocking=True); dv.copy_(src[2], non_blocking=True)
+                if axis == 0:
+                    dq.copy_(src[0], non_blocking=True); dk.copy_(src[1], non_blocking=True); dv.copy_(src[2], non_blocking=True)
+                else:      # a slice of heads: one pitched DMA per tensor
+                    for d_t, s_t in zip((dq, dk, dv), src):
+                        _copy_heads(d_t, s_t, True, pipe.s_in)
                 ev_in = torch.cuda.Event(); ev_in.record(pipe.s_in)
             cur.wait_event(ev_in)
             if ev_out[i & 1] is not None:
@@ -470,7 +491,11 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
             ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
             with torch.cuda.stream(pipe.s_out):
                 pipe.s_out.wait_event(ev_comp[i & 1])
-                dst_o.copy_(do, non_blocking=True); dst_l.copy_(dl, non_blocking=True)
+                if axis == 0:
+                    dst_o.copy_(do, non_blocking=True)
+                else:
+                    _copy_heads(dst_o, do, False, pipe.s_out)
+                dst_l.copy_(dl, non_blocking=True)
                 ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
         for e in ev_out:
             if e is not None:
