@@ -355,13 +355,19 @@ def secondary(sfa, primary, dev, peaks):
                 fn()
             torch.cuda.synchronize()
             times = []
-            for _ in range(10):
+            # flushed workloads: one call per event pair behind the flush kernel (which also hides the host's
+            # enqueue time); the others: 10 back-to-back calls per event pair, as the primary line is timed
+            inner = 1 if flush is not None else 10
+            for _ in range(10 if flush is not None else 5):
                 if flush is not None:
                     flush.zero_()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(); fn(); e1.record()
+                e0.record()
+                for _ in range(inner):
+                    fn()
+                e1.record()
                 torch.cuda.synchronize()
-                times.append(e0.elapsed_time(e1))
+                times.append(e0.elapsed_time(e1) / inner)
             ms = statistics.median(times)
             rate = units["amount"] / (ms / 1e3)
             res[name] = {"metric": units["metric"], "value": rate, "unit": units["unit"], "ms": ms,
