@@ -390,13 +390,6 @@ class _HostPipeline:
         return cls._cache[k]
 
 
-def _chunk_axis(B: int, H_kv: int, chunks: Optional[int]):
-    """Cut along the batch when it has several entries, else along the kv heads: (axis, count)."""
-    if B > 1:
-        return 0, (min(chunks, B) if chunks else min(B, 8))
-    return 2, (min(chunks, H_kv) if chunks else min(H_kv, 8))
-
-
 def _pinned(t: torch.Tensor, what: str):
     if t.is_cuda:
         raise ValueError(f"{what} must be a host tensor (use fwd()/decode() for device tensors)")
@@ -435,11 +428,16 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
         out = torch.empty(q.shape, dtype=q.dtype, pin_memory=True)
     if lse is None:
         lse = torch.empty((B, Hq, Sq), dtype=torch.float32, pin_memory=True)
-    axis, n = _chunk_axis(B, Hkv, chunks)
     g = Hq // Hkv
-    ext = B if axis == 0 else Hkv
-    step = (ext + n - 1) // n
-    cb, ch = (step, Hkv) if axis == 0 else (B, step)
+    # Chunks are (batch range) x (kv-head range).  A partial head range is moved with pitched DMAs (_copy_heads), kept
+    # at least 1 KB wide per row; 16 chunks by default (8 for one sequence) keep the exposed first upload and last
+    # download small against the PCIe time of the whole call.
+    want = chunks if chunks else (16 if B > 1 else 8)
+    n_b = max(1, min(B, want))
+    n_h = max(1, min(Hkv, want // n_b))
+    if not chunks:                      # the 1 KB floor applies to the default only: an explicit count is obeyed
+        n_h = max(1, min(n_h, (Hkv * D * q.element_size()) // 1024))
+    cb, ch = (B + n_b - 1) // n_b, (Hkv + n_h - 1) // n_h
     pipe = _HostPipeline.get(dev, ("fwd", q.dtype, cb, Sq, Sk, ch, g, D),
                              [((cb * Sq * ch * g * D,), q.dtype), ((cb * Sk * ch * D,), k.dtype),
                               ((cb * Sk * ch * D,), v.dtype), ((cb * Sq * ch * g * D,), q.dtype),
@@ -450,17 +448,13 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
         pipe.s_in.wait_event(start); pipe.s_out.wait_event(start)
         ev_comp = [None, None]      # kernel done with staging buffer i (inputs reusable)
         ev_out = [None, None]       # D2H done with staging buffer i (outputs reusable)
-        for i, lo in enumerate(range(0, ext, step)):
-            hi = min(ext, lo + step)
-            w = hi - lo
+        pieces = [(b0, min(B, b0 + cb), h0, min(Hkv, h0 + ch)) for b0 in range(0, B, cb) for h0 in range(0, Hkv, ch)]
+        for i, (b0, b1, h0, h1) in enumerate(pieces):
             fq, fk, fv, fo, fl = pipe.bufs[i & 1]
-            if axis == 0:
-                src = (q[lo:hi], k[lo:hi], v[lo:hi]); dst_o, dst_l = out[lo:hi], lse[lo:hi]
-                bs, hq_c, hk_c = w, Hq, Hkv
-            else:
-                src = (q[:, :, lo * g:hi * g], k[:, :, lo:hi], v[:, :, lo:hi])
-                dst_o, dst_l = out[:, :, lo * g:hi * g], lse[:, lo * g:hi * g]
-                bs, hq_c, hk_c = B, w * g, w
+            whole = h0 == 0 and h1 == Hkv          # every head: the rows are contiguous, plain copies
+            src = (q[b0:b1, :, h0 * g:h1 * g], k[b0:b1, :, h0:h1], v[b0:b1, :, h0:h1])
+            dst_o, dst_l = out[b0:b1, :, h0 * g:h1 * g], lse[b0:b1, h0 * g:h1 * g]
+            bs, hq_c, hk_c = b1 - b0, (h1 - h0) * g, h1 - h0
             dq = fq[: bs * Sq * hq_c * D].view(bs, Sq, hq_c, D)
             dk = fk[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
             dv = fv[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
@@ -469,7 +463,7 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
             with torch.cuda.stream(pipe.s_in):
                 if ev_comp[i & 1] is not None:
                     pipe.s_in.wait_event(ev_comp[i & 1])
-                if axis == 0:
+                if whole:
                     dq.copy_(src[0], non_blocking=True); dk.copy_(src[1], non_blocking=True); dv.copy_(src[2], non_blocking=True)
                 else:      # a slice of heads: one pitched DMA per tensor
                     for d_t, s_t in zip((dq, dk, dv), src):
@@ -491,11 +485,15 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
             ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
             with torch.cuda.stream(pipe.s_out):
                 pipe.s_out.wait_event(ev_comp[i & 1])
-                if axis == 0:
+                if whole:
                     dst_o.copy_(do, non_blocking=True)
                 else:
                     _copy_heads(dst_o, do, False, pipe.s_out)
-                dst_l.copy_(dl, non_blocking=True)
+                if bs == 1 or whole:
+                    dst_l.copy_(dl, non_blocking=True)      # contiguous on the host
+                else:
+                    for bb in range(bs):                    # (heads, Sq) blocks of different sequences
+                        dst_l[bb].copy_(dl[bb], non_blocking=True)
                 ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
         for e in ev_out:
             if e is not None:

@@ -169,7 +169,7 @@ def test_fwd_full_c2_shape_spot_check():
     _spot_check(q, k, v, o, lse, False, [0, 1000, 4095], [(0, 0), (3, 15)], dtype)
 
 
-@pytest.mark.parametrize("B,H,Hkv,chunks", [(4, 4, 2, None), (1, 8, 4, 3), (3, 2, 2, 2)])
+@pytest.mark.parametrize("B,H,Hkv,chunks", [(4, 4, 2, None), (1, 8, 4, 3), (3, 2, 2, 2), (3, 8, 4, 12), (2, 4, 4, 5)])
 def test_fwd_host_pipeline_matches_device_path(B, H, Hkv, chunks):
     """Pinned host tensors in, pinned host tensors out: the chunked three-stream pipeline must give exactly
     what one device-resident call gives (the units are independent), and match the oracle."""
