@@ -385,6 +385,14 @@ def cpu_baseline(name, budget_s=15.0):
     from oracle import naive
     kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
     units = workload_units(name)
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its ranks, which would time the
+    # reference's CPU path on one core at N > 1 (only rank 0 runs it, the other ranks do no CPU work)
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    if torch.get_num_threads() != avail:
+        torch.set_num_threads(avail)
     cores = torch.get_num_threads()
     g = torch.Generator().manual_seed(0)
     t_used, n = 0.0, 0
