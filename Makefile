@@ -16,10 +16,15 @@ example: lib
 	$(NVCC) -o build/testFlashDecoder examples/cpp/testFlashDecoder.cc -O2 -std=c++17 $(ARCH) -lineinfo \
 	  -I include -L build -lStarFlashAttention -Xlinker -rpath -Xlinker '$$ORIGIN'
 
+# C++ callers of the MANGLED entry points (run by tests/test_capi_gpu.py on the GPU box)
+cpptest: lib
+	$(NVCC) -o build/test_mangled_entry tests/cpp/test_mangled_entry.cc -O2 -std=c++17 $(ARCH) -lineinfo \
+	  -I include -L build -lStarFlashAttention -Xlinker -rpath -Xlinker '$$ORIGIN'
+
 oracle:
 	$(MAKE) -C oracle
 
 clean:
 	rm -rf build starflashattention_b200/lib
 
-.PHONY: all lib example oracle clean
+.PHONY: all lib example cpptest oracle clean

@@ -10,6 +10,8 @@ import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "lib", "libStarFlashAttention.so")
+if os.environ.get("SFA_PROBES_LIB") == "1":      # tuning tools only: the -DSFA_PROBES build (build.py --probes)
+    LIB_PATH = os.path.join(_PKG, "lib", "libStarFlashAttention_probes.so")
 
 SFA_FP16, SFA_BF16 = 0, 1
 SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 0, -1, -2, -3, -4

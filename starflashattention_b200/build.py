@@ -19,8 +19,12 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(PKG, "lib", "obj")
 LIB = os.path.join(PKG, "lib", "libStarFlashAttention.so")
+# Test / tuning build of the same sources with -DSFA_PROBES: extra prefill instantiations selectable through
+# SFA_FWD_* environment variables and the event trace.  Never loaded by the product path (SFA_PROBES_LIB=1 selects it).
+OBJ_PROBES = os.path.join(PKG, "lib", "obj_probes")
+LIB_PROBES = os.path.join(PKG, "lib", "libStarFlashAttention_probes.so")
 
-SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "capi.cu"]
+SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "fwd_sm100_v1.cu", "capi.cu"]
 HEADERS = [os.path.join(CSRC, "internal.h"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(CSRC, "rope.cuh"), os.path.join(CSRC, "merge.cuh"),
            os.path.join(ROOT, "include", "star_flash_attn.h"), os.path.join(ROOT, "include", "src", "flash_attn.h"),
            os.path.join(ROOT, "include", "src", "params.h"), os.path.join(ROOT, "include", "src", "traits.h")]
@@ -46,9 +50,9 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def _compile(src: str, verbose: bool) -> str:
-    obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-    cmd = [nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+def _compile(src: str, verbose: bool, probes: bool = False) -> str:
+    obj = os.path.join(OBJ_PROBES if probes else OBJ, src.replace(".cu", ".o"))
+    cmd = [nvcc(), *NVCC_FLAGS, *(["-DSFA_PROBES"] if probes else []), "-c", os.path.join(CSRC, src), "-o", obj]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -59,20 +63,21 @@ def _compile(src: str, verbose: bool) -> str:
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(OBJ, exist_ok=True)
+def build(force: bool = False, verbose: bool = False, probes: bool = False) -> str:
+    obj_dir, lib = (OBJ_PROBES, LIB_PROBES) if probes else (OBJ, LIB)
+    os.makedirs(obj_dir, exist_ok=True)
     todo = [s for s in SOURCES
-            if force or _stale(os.path.join(OBJ, s.replace(".cu", ".o")), [os.path.join(CSRC, s), *HEADERS])]
+            if force or _stale(os.path.join(obj_dir, s.replace(".cu", ".o")), [os.path.join(CSRC, s), *HEADERS])]
     if todo:
         with concurrent.futures.ThreadPoolExecutor(max_workers=len(todo)) as ex:
-            list(ex.map(lambda s: _compile(s, verbose), todo))
-    objs = [os.path.join(OBJ, s.replace(".cu", ".o")) for s in SOURCES]
-    if force or todo or _stale(LIB, objs):
-        cmd = [nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
+            list(ex.map(lambda s: _compile(s, verbose, probes), todo))
+    objs = [os.path.join(obj_dir, s.replace(".cu", ".o")) for s in SOURCES]
+    if force or todo or _stale(lib, objs):
+        cmd = [nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib, *objs]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    return LIB
+    return lib
 
 
 def torch_ext_path() -> str:
@@ -111,7 +116,10 @@ if __name__ == "__main__":
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--torch-ext", action="store_true", help="also build the star_flash_attn PyTorch extension")
+    ap.add_argument("--probes", action="store_true", help="also build the -DSFA_PROBES tuning library")
     a = ap.parse_args()
     print(build(a.force, a.verbose))
+    if a.probes:
+        print(build(a.force, a.verbose, probes=True))
     if a.torch_ext:
         print(build_torch_ext(a.force))

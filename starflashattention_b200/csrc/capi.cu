@@ -412,11 +412,17 @@ int sfa_fwd_watchdog(int clear) {
     if (!sfa::current_device()) return SFA_ERR_NO_DEVICE;
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return sfa::fail(SFA_ERR_CUDA, std::string("cudaDeviceSynchronize: ") + cudaGetErrorString(e));
-    int v = 0;
+    int v = 0, v1 = 0;
     int rc = sfa::fwd_error_flag_read(&v);
     if (rc) return rc;
-    if (clear && v) rc = sfa::fwd_error_flag_clear();
-    return rc ? rc : v;
+    if ((rc = sfa::fwd_error_flag_read_v1(&v1))) return rc;
+    if (clear && v) {
+        // an aborted persistent kernel may have left its schedule counters behind
+        if ((rc = sfa::fwd_error_flag_clear())) return rc;
+        rc = sfa::fwd_sched_reset();
+    }
+    if (clear && v1) rc = sfa::fwd_error_flag_clear_v1();
+    return rc ? rc : (v ? v : v1);
 }
 
 }  // extern "C"

@@ -18,11 +18,22 @@ int fail(int code, const std::string& msg) {
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
 namespace {
+// Scratch of one (device, stream): split-KV partials live here between the two launches of a decode call, so two
+// streams must never share it.  Buffers that were outgrown are kept until sfa_release_workspaces(): a CUDA graph
+// may have captured their address, and work queued earlier may still be using them.
+struct StreamScratch {
+    cudaStream_t stream = nullptr;
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+};
+constexpr int kSchedSlots = 4096;          // [0, 2048) rotate per launch, [2048, 4096) are given out once (captures)
 struct PerDevice {
     DeviceInfo info;
     bool probed = false;
-    void* ws = nullptr;
-    size_t ws_bytes = 0;
+    std::vector<StreamScratch> scratch;
+    std::vector<void*> retired;
+    int* sched = nullptr;                  // kSchedSlots x 2 ints, zero between launches
+    unsigned sched_next = 0, sched_captured = 0;
 };
 std::mutex g_mu;
 std::vector<PerDevice> g_dev;
@@ -65,27 +76,78 @@ void* get_workspace(size_t bytes, cudaStream_t stream) {
     std::lock_guard<std::mutex> lk(g_mu);
     if ((int)g_dev.size() <= dev) g_dev.resize(dev + 1);
     PerDevice& d = g_dev[dev];
-    if (d.ws_bytes >= bytes) return d.ws;
+    StreamScratch* sc = nullptr;
+    for (StreamScratch& x : d.scratch)
+        if (x.stream == stream) { sc = &x; break; }
+    if (!sc) {
+        d.scratch.push_back(StreamScratch{stream, nullptr, 0});
+        sc = &d.scratch.back();
+    }
+    if (sc->ws_bytes >= bytes) return sc->ws;
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(stream, &cap);
     if (cap != cudaStreamCaptureStatusNone) {
-        set_error("workspace must grow but the stream is being captured; warm the call up once before capture "
-                  "or pass a caller-owned workspace");
+        set_error("workspace must grow but the stream is being captured; warm the call up once on this stream "
+                  "before capture or pass a caller-owned workspace");
         return nullptr;
     }
-    // Work queued earlier may still read the old buffer.
-    cudaDeviceSynchronize();
-    if (d.ws) cudaFree(d.ws);
-    d.ws = nullptr;
-    d.ws_bytes = 0;
+    // The outgrown buffer is retired, not freed: earlier work on this stream, or a captured graph, may still use it.
+    if (sc->ws) d.retired.push_back(sc->ws);
+    sc->ws = nullptr;
+    sc->ws_bytes = 0;
     size_t want = bytes < (size_t(8) << 20) ? (size_t(8) << 20) : bytes + bytes / 4;
-    if (cudaMalloc(&d.ws, want) != cudaSuccess) {
+    if (cudaMalloc(&sc->ws, want) != cudaSuccess) {
         cudaGetLastError();
         set_error("cudaMalloc of the split-KV workspace failed");
         return nullptr;
     }
-    d.ws_bytes = want;
-    return d.ws;
+    sc->ws_bytes = want;
+    return sc->ws;
+}
+
+int* fwd_sched_counters(cudaStream_t stream) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if ((int)g_dev.size() <= dev) g_dev.resize(dev + 1);
+    PerDevice& d = g_dev[dev];
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cap);
+    if (!d.sched) {
+        if (cap != cudaStreamCaptureStatusNone) {
+            set_error("the first prefill call on a device cannot be captured in a CUDA graph; warm it up once");
+            return nullptr;
+        }
+        const size_t bytes = (size_t)kSchedSlots * 2 * sizeof(int);
+        if (cudaMalloc(reinterpret_cast<void**>(&d.sched), bytes) != cudaSuccess ||
+            cudaMemset(d.sched, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+            cudaGetLastError();
+            d.sched = nullptr;
+            set_error("allocation of the prefill schedule counters failed");
+            return nullptr;
+        }
+    }
+    unsigned slot;
+    if (cap != cudaStreamCaptureStatusNone) {
+        // a captured launch replays with the same counters for as long as its graph lives: a slot of its own
+        if (d.sched_captured >= kSchedSlots / 2) {
+            set_error("more than 2048 prefill launches captured in CUDA graphs on this device");
+            return nullptr;
+        }
+        slot = kSchedSlots / 2 + d.sched_captured++;
+    } else {
+        slot = d.sched_next++ % (kSchedSlots / 2);
+    }
+    return d.sched + 2 * slot;
+}
+
+int fwd_sched_reset() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return SFA_ERR_NO_DEVICE;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if ((int)g_dev.size() <= dev || !g_dev[dev].sched) return SFA_OK;
+    SFA_CUDA_CHECK(cudaMemset(g_dev[dev].sched, 0, (size_t)kSchedSlots * 2 * sizeof(int)));
+    return SFA_OK;
 }
 
 }  // namespace sfa
@@ -99,12 +161,15 @@ void sfa_release_workspaces(void) {
     int cur = -1;
     cudaGetDevice(&cur);
     for (size_t i = 0; i < sfa::g_dev.size(); ++i) {
-        if (!sfa::g_dev[i].ws) continue;
+        sfa::PerDevice& d = sfa::g_dev[i];
+        if (d.scratch.empty() && d.retired.empty()) continue;
         cudaSetDevice((int)i);
         cudaDeviceSynchronize();
-        cudaFree(sfa::g_dev[i].ws);
-        sfa::g_dev[i].ws = nullptr;
-        sfa::g_dev[i].ws_bytes = 0;
+        for (sfa::StreamScratch& x : d.scratch)
+            if (x.ws) cudaFree(x.ws);
+        for (void* r : d.retired) cudaFree(r);
+        d.scratch.clear();
+        d.retired.clear();
     }
     if (cur >= 0) cudaSetDevice(cur);
 }

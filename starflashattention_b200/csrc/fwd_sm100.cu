@@ -1,25 +1,31 @@
 // Prefill attention forward for sm_100a: O = softmax(Q K^T * scale [+ causal mask]) V, LSE.
 //
 // The reference has no prefill kernel; the arithmetic is the naive formula its
-// Python example runs (examples/python/testFlashDecoder.py:84 scores, :88 softmax, :92 probs @ V).
+// Python example runs (examples/python/testFlashDecoder.py:84 scores, :88 softmax, :92 probs @ V).  The loop this
+// kernel replaces is the reference's single-buffered tile loop (src/flash_attn.cu:769-843, "TODO: DoubleBuffer" :720).
 //
-// Structure (one CTA per NQ x 128 query rows of one (batch, head)):
+// Persistent kernel: one CTA per SM, each working through WORK ITEMS = (batch, head, block of NQ x 128 query rows)
+// handed out by an atomic counter in heavy-first order (see launch_fwd).  Roles inside a CTA:
 //   warps 0 .. 4*NQ-1   softmax warpgroups, one per 128-row query tile; thread i of a warpgroup owns
 //                       row i (TMEM lane i): tcgen05.ld S -> score buffer handed back -> online softmax
 //                       in fp32 (exp2 on log2e-prescaled scores, fused causal/tail masking) ->
-//                       tcgen05.st P as bf16/fp16 into the tile's own P columns -> epilogue O / l -> global
-//   warp 4*NQ           TMA producer: Q tiles once, then K_0 V_0 K_1 V_1 ... through a ring of
-//                       128-key tiles in shared memory (128-byte swizzle), mbarrier full/empty
+//                       tcgen05.st P as bf16/fp16 into the tile's own P columns; at the end of an item
+//                       O / l -> swizzled shared memory -> TMA store, LSE -> global
+//   warp 4*NQ           scheduler + TMA producer: fetches the next item (atomicAdd) one item ahead and
+//                       publishes it to the other warps, loads the item's Q tiles, then K_0 V_0 K_1 V_1 ...
+//                       through a ring of 128-key tiles (128-byte swizzle, mbarrier full/empty) that
+//                       runs on ACROSS items: the next item's Q and first tiles arrive under the current
+//                       item's last P.V and epilogue
 //   warps 4*NQ+1 ..     tcgen05 issuers, one warp per query tile (one elected lane issues):
 //                       S_q = Q_q K_j^T (SS, both operands K-major) and O_q += P_q V_j (TS: A = P in
 //                       TMEM, B = V in smem, MN-major); the first of them owns the TMEM allocation
 // TMEM: P0 P1 | S | O0 O1 = 2 x 64 + 128 + 2 x 128 columns at head_dim 128.  P does not alias S: a
 // softmax warpgroup frees the score buffer as soon as its tcgen05.ld has landed in registers, so
-// the tensor pipe computes S(q, j+1) while the warpgroup is still exponentiating tile j.  The
-// softmax warpgroups therefore run back to back (throughput bound) instead of sitting in the
-// latency chain softmax -> P.V -> Q.K(next) of an aliased S/P layout.  Issue order of tile q's MMA warp:
-// Q.K(q, j) then P.V(q, j-1), for j = 0, 1, ...  The single score buffer alternates between
+// the tensor pipe computes S(q, j+1) while the warpgroup is still exponentiating tile j.  Issue order of tile q's
+// MMA warp: Q.K(q, j) then P.V(q, j-1), for j = 0, 1, ...  The single score buffer alternates between
 // the two query tiles (head_dim 64 and the one-tile variant have room for two buffers).
+// Every mbarrier is followed by running counters (tiles, ring loads, items seen so far), not by the tile index
+// inside an item, so the pipeline never drains between items.
 // O is rescaled lazily: the reference maximum of a row only moves when the true maximum has grown
 // by more than 2^8, so the TMEM read-modify-write of O is rare after the first tiles.
 #include "internal.h"
@@ -47,19 +53,29 @@ constexpr float kRescaleThreshold = 8.0f;   // log2 units
 constexpr int kStaggerCycles64 = 1700;
 
 struct FwdParams {
-    void* o;
     float* lse;
     int* error_flag;
-    int64_t o_bs, o_rs, o_hs;
+    int* sched;           // [0] next-item counter, [1] CTAs done (both zero between launches)
     int seqlen_q, seqlen_k, heads_q, group;
-    int causal, is_bf16;
+    int causal;
     float scale_log2;
     int stagger_cycles;   // head start of warpgroup 0 over warpgroup 1 (see launch_fwd)
-    int load_order;       // 1: prologue loads go out Q0, K0, Q1, V0, ... (default); 0: Q0, Q1, K0, V0, ... (SFA_FWD_LOADORDER)
+    // work-item order: groups of `group_heads` (batch, head) pairs; inside a group query blocks from the last
+    // (heaviest under the causal mask) to the first, heads innermost
+    int m_blocks, heads_total, group_heads, total_items;
 };
 
-__device__ int g_fwd_error;
-__device__ unsigned long long g_fwd_probe[32 + 2048];   // DBG == 5: cycle counters of CTA (0,0,0), see tools/fwd_probe.py   // set when an mbarrier wait times out (pipeline bug guard)
+__device__ int g_fwd_error;   // set when an mbarrier wait times out (pipeline bug guard)
+#ifdef SFA_PROBES
+// event trace of the CTA with blockIdx.x == 0 (tools/fwd_trace.py): slot 32 + (n * 2 + q) * 16 + e holds clock64()
+// of event e of the n-th key tile this CTA processed for query tile q; slots 24.. are per-CTA stamps
+__device__ unsigned long long g_fwd_probe[32 + 4096];
+#define SFA_TRACE(cond, n, q, e) do { if ((cond) && (n) < 128) g_fwd_probe[32 + ((n) * 2 + (q)) * 16 + (e)] = clock64(); } while (0)
+#define SFA_STAMP(cond, i) do { if (cond) g_fwd_probe[i] = clock64(); } while (0)
+#else
+#define SFA_TRACE(cond, n, q, e) do { } while (0)
+#define SFA_STAMP(cond, i) do { } while (0)
+#endif
 
 // Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.
 __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
@@ -76,12 +92,6 @@ __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int*
         }
     }
     return true;
-}
-
-// DBG == 6: event trace of CTA (0,0,0): slot 32 + (j * 2 + q) * 16 + e holds clock64() of event e of tile (q, j).
-// Events 0-6 are written by the MMA warp, 8-12 by the first softmax warp of the tile's warpgroup.
-__device__ __forceinline__ void trace_event(bool on, int q, int j, int e) {
-    if (on && j < 64) g_fwd_probe[32 + (j * 2 + q) * 16 + e] = clock64();
 }
 
 // ---- packed fp32x2 arithmetic (FFMA2 / FADD2 / FMUL2 on sm_100): halves the issue slots of the softmax
@@ -197,21 +207,65 @@ struct FwdSmem {
     static constexpr int kTileBytes = (D / 64) * kSubTileBytes;      // one 128 x D tile
     static constexpr int kQOff = 0;
     static constexpr int kRingOff = NQ * kTileBytes;
-    static constexpr int kBarOff = kRingOff + NSTAGE * kTileBytes;
-    // barriers: q_full[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], pv_done[NQ], s_free[2]
-    static constexpr int kNumBars = 5 * NQ + 2 * NSTAGE + 2;
-    static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
+    // O staging for the TMA store: per query tile one 128-row x 64-column sub-tile (used D / 64 times per item)
+    static constexpr int kStageOff = kRingOff + NSTAGE * kTileBytes;
+    static constexpr int kBarOff = kStageOff + NQ * kSubTileBytes;
+    // barriers: q_full[NQ], q_empty[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], pv_done[NQ],
+    //           s_free[2], sched_full[2], sched_empty[2]
+    static constexpr int kNumBars = 6 * NQ + 2 * NSTAGE + 6;
+    static constexpr int kSchedOff = kBarOff + kNumBars * 8;         // two published item indices
+    static constexpr int kTmemPtrOff = kSchedOff + 16;
     static constexpr int kBytes = kTmemPtrOff + 16;
     static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
     static_assert(kAlloc <= 232448, "shared memory budget exceeded");
 };
 
+// One work item: NQ query tiles of one (batch, head).
+template <int NQ>
+struct Item {
+    int m0, h, b, hk;
+    int n[NQ];      // key tiles each query tile needs (causal: up to the diagonal of its last row)
+    int n_max;
+};
+
+template <int NQ>
+__device__ __forceinline__ void decode_item(const FwdParams& p, int idx, Item<NQ>& it) {
+    const int per_group = p.group_heads * p.m_blocks;
+    const int g = idx / per_group;
+    const int r = idx - g * per_group;
+    const int head0 = g * p.group_heads;
+    const int gh = min(p.group_heads, p.heads_total - head0);
+    const int m_desc = r / gh;
+    const int head = head0 + (r - m_desc * gh);
+    const int m_block = p.m_blocks - 1 - m_desc;
+    it.b = head / p.heads_q;
+    it.h = head - it.b * p.heads_q;
+    it.hk = it.h / p.group;
+    it.m0 = m_block * (NQ * kBlockM);
+    const int kv_tiles_total = (p.seqlen_k + kBlockN - 1) / kBlockN;
+    const int causal_shift = p.seqlen_k - p.seqlen_q;   // query i sees keys <= i + shift
+    it.n_max = 0;
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        int n = kv_tiles_total;
+        if (p.causal) {
+            const int last_row = min(it.m0 + (q + 1) * kBlockM, p.seqlen_q) - 1;
+            const int last_key = last_row + causal_shift;
+            n = last_key < 0 ? 0 : min(kv_tiles_total, last_key / kBlockN + 1);
+        }
+        if (it.m0 + q * kBlockM >= p.seqlen_q) n = 0;   // tile entirely past the end of Q
+        it.n[q] = n;
+        it.n_max = max(it.n_max, n);
+    }
+}
+
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-// DBG: 0 = product; 1, 2, 4 = timing probes that give wrong results, 5 = cycle counters (tools/fwd_time.py).
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
+// SOFTREL: ring slots are handed back by the softmax warpgroups (plain arrive once they have seen the
+// MMA's completion barrier) instead of by two more tcgen05.commit per tile from the MMA warps.
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, bool SOFTREL>
 __global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
-           const __grid_constant__ CUtensorMap v_map, const FwdParams p) {
+           const __grid_constant__ CUtensorMap v_map, const __grid_constant__ CUtensorMap o_map, const FwdParams p) {
     using L = FwdSmem<D, NQ, NSTAGE>;
     using R = FwdRegs<NQ>;
     using T = FwdTmem<D, NQ>;
@@ -219,121 +273,62 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     constexpr int kSoftmaxWarps = 4 * NQ;
     constexpr int kSBufs = T::kSBufs;
     constexpr int kSub = D / 64;
-    constexpr bool kFreeRun = DBG == 4;   // probe: the MMA warp never waits for the softmax warps
-    constexpr bool kProbe = DBG == 4 || DBG == 5;
-    constexpr bool kTrace = DBG == 6;
+    constexpr int kSchedConsumers = 5 * NQ;   // softmax warps + MMA warps
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
     const uint32_t bar_base = smem_base + L::kBarOff;
     auto bar_q_full = [&](int q) { return bar_base + 8u * q; };
-    auto bar_kv_full = [&](int s) { return bar_base + 8u * (NQ + s); };
-    auto bar_kv_empty = [&](int s) { return bar_base + 8u * (NQ + NSTAGE + s); };
-    auto bar_s_full = [&](int q) { return bar_base + 8u * (NQ + 2 * NSTAGE + q); };
+    // every Q.K of the item that reads Q tile q has completed: the tile may be overwritten by the next item's
+    auto bar_q_empty = [&](int q) { return bar_base + 8u * (NQ + q); };
+    auto bar_kv_full = [&](int s) { return bar_base + 8u * (2 * NQ + s); };
+    auto bar_kv_empty = [&](int s) { return bar_base + 8u * (2 * NQ + NSTAGE + s); };
+    auto bar_s_full = [&](int q) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + q); };
     // P is handed to the MMA warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
-    auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + 2 * q + half); };
+    auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (3 * NQ + 2 * NSTAGE + 2 * q + half); };
     // every P.V of query tile q has completed: P(q) may be overwritten, O(q) may be rescaled / read
-    auto bar_pv_done = [&](int q) { return bar_base + 8u * (4 * NQ + 2 * NSTAGE + q); };
+    auto bar_pv_done = [&](int q) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + q); };
     // warpgroup q has loaded its scores into registers: the next Q.K may overwrite that buffer
-    auto bar_s_free = [&](int q) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + q); };
+    auto bar_s_free = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + i); };
+    auto bar_sched_full = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 2 + i); };
+    auto bar_sched_empty = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 4 + i); };
+    volatile int* sched_slot = reinterpret_cast<volatile int*>(smem_gen + L::kSchedOff);
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // DBG == 6: prologue / epilogue stamps of CTA (0,0,0): 24 kernel entry, 25 set-up done, 26 last P.V seen by
-    // warpgroup 0, 27 its O rows stored, 28 teardown
-    const bool stamp = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0;
-    if (stamp) g_fwd_probe[24] = clock64();
-    // Heavy (late) query blocks first: under the causal mask they own the most key tiles.
-    const int m_block = gridDim.x - 1 - blockIdx.x;
-    const int h = blockIdx.y, b = blockIdx.z;
-    const int hk = h / p.group;
-    const int m0 = m_block * (NQ * kBlockM);
-    const int kv_tiles_total = (p.seqlen_k + kBlockN - 1) / kBlockN;
-    const int causal_shift = p.seqlen_k - p.seqlen_q;   // query i sees keys <= i + shift
-
-    // Key tiles each query tile needs (causal: up to the diagonal of its last row).
-    int n_tiles[NQ];
-    int n_max = 0;
-#pragma unroll
-    for (int q = 0; q < NQ; ++q) {
-        int n = kv_tiles_total;
-        if (p.causal) {
-            const int last_row = min(m0 + (q + 1) * kBlockM, p.seqlen_q) - 1;
-            const int last_key = last_row + causal_shift;
-            n = last_key < 0 ? 0 : min(kv_tiles_total, last_key / kBlockN + 1);
-        }
-        if (m0 + q * kBlockM >= p.seqlen_q) n = 0;   // tile entirely past the end of Q
-        n_tiles[q] = n;
-        n_max = max(n_max, n);
-    }
-    // Q.K products are ordered j-major, q-minor; the k-th one writes score buffer k % kSBufs.
-    auto qk_ordinal = [&](int q, int j) {
-        int k = 0;
-#pragma unroll
-        for (int qq = 0; qq < NQ; ++qq) k += min(j, n_tiles[qq]) + ((qq < q && j < n_tiles[qq]) ? 1 : 0);
-        return k;
-    };
-    // inverse of qk_ordinal: (query tile << 16) | key tile
-    auto tile_of_ordinal = [&](int ord) {
-        const int n0 = n_tiles[0], n1 = n_tiles[NQ - 1], m = min(n0, n1);
-        if (ord < 2 * m) return ((ord & 1) << 16) | (ord >> 1);
-        return ((n0 > n1 ? 0 : 1) << 16) | (m + ord - 2 * m);
-    };
-    // Score buffer of tile (q, j): the single shared buffer (two query tiles at head_dim 128), else one buffer
-    // per query tile, else (one query tile) alternating buffers.
-    auto s_buffer = [&](int q, int j) { return kSBufs == 1 ? 0 : (NQ == 2 ? q : (j & 1)); };
-    // Barrier on which the warpgroup of tile (q, j) reports "scores loaded, buffer free".  Every barrier has
-    // exactly one waiter at a time and that waiter follows each of its phases in order, which is what a parity
-    // wait needs: per warpgroup when the buffer is shared or dedicated, per buffer when one tile alternates.
-    auto s_free_index = [&](int q, int j) { return NQ == 2 ? q : (j & 1); };
+    const int causal_shift = p.seqlen_k - p.seqlen_q;
+#ifdef SFA_PROBES
+    const bool trace_cta = blockIdx.x == 0;
+#endif
+    SFA_STAMP(trace_cta && threadIdx.x == 0, 24);
 
     if (warp == kSoftmaxWarps && lane == 0) {
         prefetch_tensormap(&q_map);
         prefetch_tensormap(&k_map);
         prefetch_tensormap(&v_map);
+        prefetch_tensormap(&o_map);
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
             mbar_init(bar_q_full(q), 1);
+            mbar_init(bar_q_empty(q), 1);
             mbar_init(bar_s_full(q), 1);
             mbar_init(bar_p_ready(q, 0), 4);   // one elected arrival per softmax warp of the tile's warpgroup
             mbar_init(bar_p_ready(q, 1), 4);
             mbar_init(bar_pv_done(q), 1);
         }
-        mbar_init(bar_s_free(0), 4);
-        mbar_init(bar_s_free(1), 4);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar_s_free(i), 4);
+            mbar_init(bar_sched_full(i), 1);
+            mbar_init(bar_sched_empty(i), kSchedConsumers);
+        }
 #pragma unroll
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bar_kv_full(s), 1);
-            mbar_init(bar_kv_empty(s), NQ);   // one arrival per query tile's MMA warp
+            mbar_init(bar_kv_empty(s), NQ);   // one arrival per query tile
         }
         fence_barrier_init();
-        // The first loads need nobody's consent (the ring starts empty): issue them before the CTA-wide sync so
-        // that their latency overlaps the TMEM allocation and the rest of the prologue.
-        // Issue order Q0, K0, then the rest: the first Q.K needs exactly those two tiles (measured on CTA (0,0,0):
-        // 5250 cycles from set-up to the first Q.K issue, all of it waiting for these loads).
-        auto load_q = [&](int q) {
-            if (n_tiles[q] == 0) return;
-            mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
-#pragma unroll
-            for (int s = 0; s < kSub; ++s)
-                tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
-                            64 * s, h, m0 + q * kBlockM, b);
-        };
-        auto load_kv = [&](int i) {
-            mbar_arrive_expect_tx(bar_kv_full(i), L::kTileBytes);
-            const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
-#pragma unroll
-            for (int s = 0; s < kSub; ++s)
-                tma_load_4d(smem_base + L::kRingOff + i * L::kTileBytes + s * L::kSubTileBytes, map, bar_kv_full(i),
-                            64 * s, hk, (i >> 1) * kBlockN, b);
-        };
-        const int n_pre = min(NSTAGE, 2 * n_max);
-        load_q(0);
-        if (p.load_order && n_pre > 0) load_kv(0);
-#pragma unroll
-        for (int q = 1; q < NQ; ++q) load_q(q);
-        for (int i = p.load_order ? 1 : 0; i < n_pre; ++i) load_kv(i);
     }
     if (warp == kSoftmaxWarps + 1) {
         tmem_alloc(smem_base + L::kTmemPtrOff, T::kCols);
@@ -343,27 +338,104 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
-    if (stamp) g_fwd_probe[25] = clock64();
+    SFA_STAMP(trace_cta && threadIdx.x == 0, 25);
 
-    // NQ == 2 runs three full warpgroups (the third holds the TMA and MMA warps plus two idle
-    // warps) so the register file can be re-split: the softmax warpgroups take what the others give up.
-    if (warp == kSoftmaxWarps) {
-        // =============================================================== TMA producer
-        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
-        // whole warp in the loop (uniform control flow), one elected lane issues; Q and the first NSTAGE
-        // tiles were issued in the prologue
-        for (int i = NSTAGE; i < 2 * n_max; ++i) {
-            const int slot = i % NSTAGE, use = i / NSTAGE;
-            if (!__all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use & 1) ^ 1, p.error_flag, 1))) break;
-            if (elect_one()) {
-                mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
-                const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+    // Q.K products of an item are ordered j-major, q-minor; the k-th one writes score buffer k % kSBufs.
+    auto qk_ordinal = [&](const Item<NQ>& it, int q, int j) {
+        int k = 0;
 #pragma unroll
-                for (int s = 0; s < kSub; ++s)
-                    tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
-                                bar_kv_full(slot), 64 * s, hk, (i >> 1) * kBlockN, b);
+        for (int qq = 0; qq < NQ; ++qq) k += min(j, it.n[qq]) + ((qq < q && j < it.n[qq]) ? 1 : 0);
+        return k;
+    };
+    // inverse of qk_ordinal (two query tiles): (query tile << 16) | key tile
+    auto tile_of_ordinal = [&](const Item<NQ>& it, int ord) {
+        const int n0 = it.n[0], n1 = it.n[NQ - 1], m = min(n0, n1);
+        if (ord < 2 * m) return ((ord & 1) << 16) | (ord >> 1);
+        return ((n0 > n1 ? 0 : 1) << 16) | (m + ord - 2 * m);
+    };
+    // how many query tiles of the item read key tile j
+    auto users = [&](const Item<NQ>& it, int j) {
+        int u = 0;
+#pragma unroll
+        for (int qq = 0; qq < NQ; ++qq) u += j < it.n[qq] ? 1 : 0;
+        return u;
+    };
+    // Consumer side of the schedule: the k-th item of this CTA (index >= total_items ends the loop).
+    auto next_item = [&](int k, bool& ok) {
+        ok = __all_sync(0xffffffffu, wait_barrier(bar_sched_full(k & 1), (k >> 1) & 1, p.error_flag, 12)) != 0;
+        const int item = sched_slot[k & 1];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_sched_empty(k & 1));
+        return ok ? item : INT_MAX;
+    };
+
+    // NQ == 2 runs three full warpgroups (the third holds the TMA and MMA warps plus one idle
+    // warp) so the register file can be re-split: the softmax warpgroups take what the others give up.
+    if (warp == kSoftmaxWarps) {
+        // =============================================================== scheduler + TMA producer
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
+        // whole warp in the loop (uniform control flow), one elected lane issues
+        int item = blockIdx.x;      // the first item is static, the later ones come from the counter
+        uint32_t ring = 0;          // K/V tiles loaded so far (all items)
+        int q_loads[NQ];            // Q tiles loaded so far, per query tile
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) q_loads[q] = 0;
+        bool ok = true;
+        for (int k = 0; ok; ++k) {
+            if (k >= 2) ok = __all_sync(0xffffffffu, wait_barrier(bar_sched_empty(k & 1), ((k >> 1) - 1) & 1, p.error_flag, 13)) != 0;
+            if (!ok) break;
+            if (lane == 0) {
+                sched_slot[k & 1] = item;
+                mbar_arrive(bar_sched_full(k & 1));
             }
             __syncwarp();
+            if (item >= p.total_items) break;
+            int nxt = 0;
+            if (lane == 0) nxt = (int)gridDim.x + atomicAdd(p.sched, 1);   // used one item later: its latency is hidden
+            Item<NQ> it;
+            decode_item<NQ>(p, item, it);
+            auto load_q = [&](int q) {
+                if (it.n[q] == 0) return;
+                if (q_loads[q] >= 1)
+                    ok = ok && __all_sync(0xffffffffu, wait_barrier(bar_q_empty(q), (q_loads[q] - 1) & 1, p.error_flag, 11)) != 0;
+                if (ok && elect_one()) {
+                    mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
+#pragma unroll
+                    for (int s = 0; s < kSub; ++s)
+                        tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
+                                    64 * s, it.h, it.m0 + q * kBlockM, it.b);
+                }
+                __syncwarp();
+                ++q_loads[q];
+            };
+            auto load_kv = [&](int i) {   // i-th K/V tile of the item: K_0 V_0 K_1 V_1 ...
+                const uint32_t gi = ring + (uint32_t)i, slot = gi % NSTAGE, use = gi / NSTAGE;
+                if (use >= 1)
+                    ok = ok && __all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use - 1) & 1, p.error_flag, 1)) != 0;
+                if (ok && elect_one()) {
+                    mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
+                    const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
+#pragma unroll
+                    for (int s = 0; s < kSub; ++s)
+                        tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
+                                    bar_kv_full(slot), 64 * s, it.hk, (i >> 1) * kBlockN, it.b);
+                }
+                __syncwarp();
+            };
+            // Q0, K0 first: the item's first Q.K needs exactly those two
+            load_q(0);
+            if (it.n_max > 0) load_kv(0);
+#pragma unroll
+            for (int q = 1; q < NQ; ++q) load_q(q);
+            for (int i = 1; i < 2 * it.n_max && ok; ++i) load_kv(i);
+            ring += 2u * (uint32_t)it.n_max;
+            item = __shfl_sync(0xffffffffu, nxt, 0);
+        }
+        // Last CTA out rezeroes the schedule counters for the next launch that uses this slot.
+        if (lane == 0) {
+            __threadfence();
+            const unsigned old = atomicInc(reinterpret_cast<unsigned*>(p.sched + 1), gridDim.x - 1);
+            if (old == gridDim.x - 1) p.sched[0] = 0;
         }
     } else if (warp > kSoftmaxWarps && warp <= kSoftmaxWarps + NQ) {
         // =============================================================== tcgen05 issuers, one warp per query tile
@@ -380,10 +452,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
         bool ok = true;
         const int q = NQ == 1 ? 0 : warp - (kSoftmaxWarps + 1);   // the query tile this warp issues for
-        const int n_q = q == 0 ? n_tiles[0] : n_tiles[NQ - 1];
         const uint64_t q_desc = smem_desc_at(desc_kmajor, smem_base + L::kQOff + q * L::kTileBytes);
         // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
-        auto issue_qk = [&](int slot, int buf) {
+        auto issue_qk = [&](uint32_t slot, int buf) {
             const uint64_t k_desc = ring_k_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
             const uint32_t s_tmem = tmem_base + T::kSOff + buf * kBlockN;
 #pragma unroll
@@ -392,7 +463,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 mma_ss(s_tmem, q_desc + off16, k_desc + off16, idesc_qk, kc > 0);
             }
         };
-        auto issue_pv = [&](int slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
+        auto issue_pv = [&](uint32_t slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
             const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
             const uint32_t p_tmem = tmem_base + T::kPOff + q * (kBlockN / 2);
             const uint32_t o_tmem = tmem_base + T::kOOff + q * D;
@@ -405,83 +476,100 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
             return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
         };
-        // A ring slot is handed back with one arrival per query tile; where the other tile does not use key tile
-        // j (causal tail, or a query tile past the end of Q) this warp arrives for it as well.
-        auto users = [&](int j) {
-            int u = 0;
+        uint32_t ring = 0;          // K/V tiles of earlier items
+        uint32_t tiles[NQ];         // key tiles each query tile has been through in earlier items
 #pragma unroll
-            for (int qq = 0; qq < NQ; ++qq) u += j < n_tiles[qq] ? 1 : 0;
-            return u;
-        };
-        long long mt_p = 0, mt_kv = 0, mt_sfree = 0, mt_total = clock64(), c0 = 0;
-        const bool tre = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
-        const bool tr = tre && lane == 0;
-        if (n_q > 0) ok = wait_all(bar_q_full(q), 0, 3);
-        for (int j = 0; j <= n_q && ok; ++j) {
-            // ---- S(q, j) = Q_q K_j^T
-            if (j < n_q) {
-                const int ki = 2 * j, kslot = ki % NSTAGE;
-                const int ord = qk_ordinal(q, j), buf = s_buffer(q, j);
-                trace_event(tr, q, j, 7);
-                if constexpr (kProbe) c0 = clock64();
-                ok = wait_all(bar_kv_full(kslot), (ki / NSTAGE) & 1, 2);
-                if constexpr (kProbe) { mt_kv += clock64() - c0; c0 = clock64(); }
-                trace_event(tr, q, j, 0);
-                if constexpr (!kFreeRun) {
+        for (int qq = 0; qq < NQ; ++qq) tiles[qq] = 0;
+        int q_uses = 0;             // items that loaded Q tile q
+        // the last Q.K of the previous non-empty item (the single shared score buffer is handed on across items)
+        bool has_last = false;
+        int last_q = 0;
+        uint32_t last_parity = 0;
+#ifdef SFA_PROBES
+        const bool tr = trace_cta && lane == 0;
+#endif
+        for (int k = 0; ok; ++k) {
+            const int item = next_item(k, ok);
+            if (item >= p.total_items) break;
+            Item<NQ> it;
+            decode_item<NQ>(p, item, it);
+            const int n_q = it.n[q];
+            if (n_q > 0) {
+                ok = wait_all(bar_q_full(q), q_uses & 1, 3);
+                ++q_uses;
+            }
+            for (int j = 0; j <= n_q && ok; ++j) {
+                // ---- S(q, j) = Q_q K_j^T
+                if (j < n_q) {
+                    const uint32_t gi = ring + 2u * (uint32_t)j, kslot = gi % NSTAGE;
+                    const uint32_t t = tiles[q] + (uint32_t)j;      // running tile count of this query tile
+                    int buf = 0;
+                    ok = wait_all(bar_kv_full(kslot), (gi / NSTAGE) & 1, 2);
+                    SFA_TRACE(tr, t, q, 0);
                     // the buffer's previous scores must have been loaded into registers by their warpgroup
                     if constexpr (NQ == 2 && kSBufs == 1) {
+                        const int ord = qk_ordinal(it, q, j);
                         if (ord >= 1) {
-                            const int prev = tile_of_ordinal(ord - 1);
-                            ok = ok && wait_all(bar_s_free(prev >> 16), prev & 1, 9);
+                            const int prev = tile_of_ordinal(it, ord - 1);
+                            const int pq = prev >> 16;
+                            ok = ok && wait_all(bar_s_free(pq), (tiles[pq] + (uint32_t)(prev & 0xffff)) & 1, 9);
+                        } else if (has_last) {
+                            ok = ok && wait_all(bar_s_free(last_q), last_parity, 9);
                         }
                     } else if constexpr (NQ == 2) {
-                        if (j >= 1) ok = ok && wait_all(bar_s_free(q), (j - 1) & 1, 9);
+                        buf = q;
+                        if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
                     } else {
-                        if (j >= 2) ok = ok && wait_all(bar_s_free(j & 1), ((j >> 1) - 1) & 1, 9);
+                        buf = t & 1;
+                        if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
                     }
+                    tc_fence_after();
+                    SFA_TRACE(tr, t, q, 1);
+                    if (ok && elect_one()) {
+                        issue_qk(kslot, buf);
+                        tc_commit(bar_s_full(q));
+                        if (j == n_q - 1) tc_commit(bar_q_empty(q));
+                        if constexpr (!SOFTREL)
+                            for (int u = users(it, j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
+                    }
+                    __syncwarp();
+                    SFA_TRACE(tr, t, q, 2);
                 }
-                if constexpr (kProbe) mt_sfree += clock64() - c0;
-                tc_fence_after();
-                trace_event(tr, q, j, 1);
-                if (ok && elect_one()) {
-                    issue_qk(kslot, buf);
-                    trace_event(tre, q, j, 13);
-                    tc_commit(bar_s_full(q));
-                    for (int u = users(j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
+                // ---- O(q) += P(q, j-1) V_{j-1}, in two halves of 64 keys
+                if (ok && j > 0) {
+                    const uint32_t gi = ring + 2u * (uint32_t)(j - 1) + 1u, vslot = gi % NSTAGE;
+                    const uint32_t t = tiles[q] + (uint32_t)(j - 1);
+                    ok = wait_all(bar_kv_full(vslot), (gi / NSTAGE) & 1, 4);
+                    ok = ok && wait_all(bar_p_ready(q, 0), t & 1, 5);
+                    tc_fence_after();
+                    SFA_TRACE(tr, t, q, 3);
+                    if (ok && elect_one()) issue_pv(vslot, 0, j > 1);
+                    __syncwarp();
+                    ok = ok && wait_all(bar_p_ready(q, 1), t & 1, 5);
+                    tc_fence_after();
+                    SFA_TRACE(tr, t, q, 5);
+                    if (ok && elect_one()) {
+                        issue_pv(vslot, 1, true);
+                        tc_commit(bar_pv_done(q));
+                        if constexpr (!SOFTREL)
+                            for (int u = users(it, j - 1); u <= NQ; ++u) tc_commit(bar_kv_empty(vslot));
+                    }
+                    __syncwarp();
+                    SFA_TRACE(tr, t, q, 6);
                 }
-                __syncwarp();
-                trace_event(tr, q, j, 2);
             }
-            // ---- O(q) += P(q, j-1) V_{j-1}, in two halves of 64 keys
-            if (ok && j > 0) {
-                const int vi = 2 * j - 1, vslot = vi % NSTAGE;
-                if constexpr (kProbe) c0 = clock64();
-                ok = wait_all(bar_kv_full(vslot), (vi / NSTAGE) & 1, 4);
-                if constexpr (kProbe) { mt_kv += clock64() - c0; c0 = clock64(); }
-                trace_event(tr, q, j - 1, 14);
-                if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 0), (j - 1) & 1, 5);
-                tc_fence_after();
-                trace_event(tr, q, j - 1, 3);
-                if (ok && elect_one()) issue_pv(vslot, 0, j > 1);
-                __syncwarp();
-                trace_event(tr, q, j - 1, 4);
-                if constexpr (!kFreeRun) ok = ok && wait_all(bar_p_ready(q, 1), (j - 1) & 1, 5);
-                if constexpr (kProbe) mt_p += clock64() - c0;
-                tc_fence_after();
-                trace_event(tr, q, j - 1, 5);
-                if (ok && elect_one()) {
-                    issue_pv(vslot, 1, true);
-                    trace_event(tre, q, j - 1, 15);
-                    tc_commit(bar_pv_done(q));
-                    for (int u = users(j - 1); u <= NQ; ++u) tc_commit(bar_kv_empty(vslot));
+            if constexpr (NQ == 2 && kSBufs == 1) {
+                const int total = it.n[0] + it.n[NQ - 1];
+                if (total > 0) {
+                    const int lt = tile_of_ordinal(it, total - 1);
+                    last_q = lt >> 16;
+                    last_parity = (tiles[last_q] + (uint32_t)(lt & 0xffff)) & 1;
+                    has_last = true;
                 }
-                __syncwarp();
-                trace_event(tr, q, j - 1, 6);
             }
-        }
-        if (kProbe && q == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
-            g_fwd_probe[16] = mt_p; g_fwd_probe[17] = mt_sfree; g_fwd_probe[18] = mt_kv;
-            g_fwd_probe[19] = clock64() - mt_total; g_fwd_probe[20] = n_q;
+#pragma unroll
+            for (int qq = 0; qq < NQ; ++qq) tiles[qq] += (uint32_t)it.n[qq];
+            ring += 2u * (uint32_t)it.n_max;
         }
     } else if (warp < kSoftmaxWarps) {
         // =============================================================== softmax warpgroups
@@ -490,22 +578,23 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         constexpr int kCols = kBlockN;
         const int q = warp >> 2;
         const int row_in_tile = (warp & 3) * 32 + lane;
-        const int row = m0 + q * kBlockM + row_in_tile;
+        const bool wg_leader = (warp & 3) == 0 && lane == 0;   // issues the TMA stores, hands ring slots back
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t p_tmem = lane_base + T::kPOff + q * (kBlockN / 2);   // my packed P columns
         const uint32_t o_tmem = lane_base + T::kOOff + q * D;
-        const int n_q = q == 0 ? n_tiles[0] : n_tiles[NQ - 1];
-        const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
+        const uint32_t stage = smem_base + L::kStageOff + q * L::kSubTileBytes;
         const float sl2 = p.scale_log2;
         const uint64_t sl2_2 = pack_f2(sl2, sl2);
-
-        float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
-        uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
         bool ok = true;
-
-        const bool probe = DBG == 5 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
-        long long pt_wait = 0, pt_max = 0, pt_exp = 0, pt_pv = 0, pt0 = 0, pt1 = 0, pt2 = 0;
-        const bool tr = kTrace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp & 3) == 0;
+        uint32_t tiles = 0;         // key tiles this warpgroup has been through in earlier items
+        uint32_t ring = 0;          // K/V tiles of earlier items
+#ifdef SFA_PROBES
+        const bool tr = trace_cta && lane == 0 && (warp & 3) == 0;
+#endif
+        auto release = [&](const Item<NQ>& it, uint32_t gi, int j) {   // hand a ring slot back (SOFTREL)
+            if (wg_leader)
+                for (int u = users(it, j); u <= NQ; ++u) mbar_arrive(bar_kv_empty(gi % NSTAGE));
+        };
         // With a score buffer of their own (head_dim 64) nothing couples the two warpgroups, and started together
         // they stay in lockstep: both in the exp2 loop (MUFU contended), then both in the load + max phase (MUFU
         // idle).  A head start for warpgroup 0 puts one's exp2 loop under the other's max phase.
@@ -513,16 +602,26 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             const long long t0 = clock64();
             while (clock64() - t0 < p.stagger_cycles) __nanosleep(64);
         }
-        for (int j = 0; j < (kFreeRun ? 0 : n_q) && ok; ++j) {
-            if constexpr (DBG == 5) pt0 = clock64();
-            const int buf = s_buffer(q, j);
-            const uint32_t s_tmem = lane_base + T::kSOff + buf * kBlockN;
-            ok = wait_barrier(bar_s_full(q), j & 1, p.error_flag, 7);
-            tc_fence_after();
-            if constexpr (DBG == 5) pt1 = clock64();
-            trace_event(tr, q, j, 8);
-            uint32_t su[kCols];
-            if constexpr (DBG != 2) {
+        for (int k = 0; ok; ++k) {
+            const int item = next_item(k, ok);
+            if (item >= p.total_items) break;
+            Item<NQ> it;
+            decode_item<NQ>(p, item, it);
+            const int n_q = it.n[q];
+            const int row = it.m0 + q * kBlockM + row_in_tile;
+            const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
+            float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
+            uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
+
+            for (int j = 0; j < n_q && ok; ++j) {
+                const uint32_t t = tiles + (uint32_t)j;
+                const int buf = kSBufs == 1 ? 0 : (NQ == 2 ? q : (int)(t & 1));
+                const int free_idx = NQ == 2 ? q : (int)(t & 1);
+                const uint32_t s_tmem = lane_base + T::kSOff + buf * kBlockN;
+                ok = wait_barrier(bar_s_full(q), t & 1, p.error_flag, 7);
+                tc_fence_after();
+                SFA_TRACE(tr, t, q, 8);
+                uint32_t su[kCols];
 #pragma unroll
                 for (int c = 0; c < kCols; c += 32) tmem_ld32(s_tmem + c, &su[c]);
                 // The buffer goes back the moment the loads have landed: its turnaround sits on the critical
@@ -530,180 +629,169 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 tmem_wait_ld();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
-                trace_event(tr, q, j, 9);
-            }
-            const int key0 = j * kBlockN;
-            const bool need_mask = (key0 + kBlockN - 1 > m0 + q * kBlockM + causal_shift && p.causal) ||
-                                   (key0 + kBlockN > p.seqlen_k);
-            const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
-            // ---- row maximum: four independent chains
-            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-            auto scan_half = [&](int base) {
-                if (need_mask) {
+                if (lane == 0) mbar_arrive(bar_s_free(free_idx));
+                if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)j, j);   // Q.K(q, j) is done with K_j
+                SFA_TRACE(tr, t, q, 9);
+                const int key0 = j * kBlockN;
+                const bool need_mask = (key0 + kBlockN - 1 > it.m0 + q * kBlockM + causal_shift && p.causal) ||
+                                       (key0 + kBlockN > p.seqlen_k);
+                const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
+                // ---- row maximum: four independent chains
+                float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                auto scan_half = [&](int base) {
+                    if (need_mask) {
 #pragma unroll
-                    for (int c = base; c < base + kCols / 2; ++c)
-                        if (c > lim) su[c] = 0xff800000u;   // -inf
-                }
-#pragma unroll
-                for (int c = base; c < base + kCols / 2; c += 2)
-                    mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
-            };
-            if constexpr (DBG != 2) scan_half(0);
-            if constexpr (DBG == 2) {      // pipeline probe: no softmax work at all
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_s_free(s_free_index(q, j)));
-                if (j > 0) ok = wait_barrier(bar_pv_done(q), (j - 1) & 1, p.error_flag, 8);
-                if (lane == 0) {
-                    mbar_arrive(bar_p_ready(q, 0));
-                    mbar_arrive(bar_p_ready(q, 1));
-                }
-                continue;
-            }
-            scan_half(kCols / 2);
-            const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-
-            // P(q, j-1) is still being read by the tensor pipe, and O(q) still accumulated into, until pv_done
-            bool pv_waited = j == 0;
-            auto wait_pv = [&]() {
-                if (!pv_waited) {
-                    long long c0 = 0;
-                    if constexpr (DBG == 5) c0 = clock64();
-                    ok = wait_barrier(bar_pv_done(q), (j - 1) & 1, p.error_flag, 8);
-                    tc_fence_after();
-                    pv_waited = true;
-                    if constexpr (DBG == 5) pt_pv += clock64() - c0;
-                }
-            };
-            const float m_new = fmaxf(m_used, mx_all);
-            if (j == 0) {
-                m_used = m_new;
-            } else {
-                const bool grow = (m_new - m_used) * sl2 > kRescaleThreshold;   // false for -inf - -inf (NaN)
-                if (__any_sync(0xffffffffu, grow)) {
-                    wait_pv();
-                    const float alpha = grow ? ex2((m_used - m_new) * sl2) : 1.f;
-                    const uint64_t alpha2 = pack_f2(alpha, alpha);
-                    l_acc[0] = fmul2(l_acc[0], alpha2);
-                    l_acc[1] = fmul2(l_acc[1], alpha2);
-                    if (grow) m_used = m_new;
-#pragma unroll
-                    for (int c = 0; c < D / 16; ++c) {   // 16-column chunks: the scores stay in registers
-                        uint32_t o[16];
-                        tmem_ld16(o_tmem + 16 * c, o);
-                        tmem_wait_ld();
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                        tmem_st16(o_tmem + 16 * c, o);
+                        for (int c = base; c < base + kCols / 2; ++c)
+                            if (c > lim) su[c] = 0xff800000u;   // -inf
                     }
-                }
-            }
-            const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
-            const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
-            if constexpr (DBG == 5) pt2 = clock64();
-            trace_event(tr, q, j, 10);
-            // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
-            // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
-            auto exp_and_store = [&](auto poly_tag) {
-                constexpr int kPoly = decltype(poly_tag)::value;
-                constexpr int kPairs = kCols / 2;
-                constexpr int kAhead = 3;            // pairs between the scale FFMA2 and its MUFUs
-                uint64_t xq[kAhead];                 // scaled scores waiting for their exp2
-                auto scale = [&](int i) {
-                    return ffma2_v(pack_f2(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), sl2_2, neg_m2);
+#pragma unroll
+                    for (int c = base; c < base + kCols / 2; c += 2)
+                        mx[(c >> 1) & 3] = fmaxf(mx[(c >> 1) & 3], fmaxf(__uint_as_float(su[c]), __uint_as_float(su[c + 1])));
                 };
-#pragma unroll
-                for (int i = 0; i < kAhead; ++i) xq[i] = scale(i);
-                uint32_t pk[32];
-#pragma unroll
-                for (int i = 0; i < kPairs; ++i) {
-                    float x0, x1, p0, p1;
-                    unpack_f2(xq[i % kAhead], x0, x1);
-                    if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
-                    if constexpr (DBG == 1) {
-                        p0 = x0; p1 = x1;
-                    } else if ((i & 7) >= 8 - kPoly) {
-                        unpack_f2(exp2_poly2(x0, x1), p0, p1);
-                    } else {
-                        p0 = ex2_v(x0); p1 = ex2_v(x1);
+                scan_half(0);
+                scan_half(kCols / 2);
+                const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+
+                // P(q, j-1) is still being read by the tensor pipe, and O(q) still accumulated into, until pv_done
+                bool pv_waited = j == 0;
+                auto wait_pv = [&]() {
+                    if (!pv_waited) {
+                        ok = wait_barrier(bar_pv_done(q), (t - 1) & 1, p.error_flag, 8);
+                        tc_fence_after();
+                        pv_waited = true;
+                        if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)(j - 1) + 1u, j - 1);   // V_{j-1}
                     }
-                    l_acc[i & 1] = fadd2_v(l_acc[i & 1], pack_f2(p0, p1));
-                    pk[i & 31] = pack_pair<BF16>(p0, p1);
-                    if ((i & 31) == 31) {
-                        if (i == 31) wait_pv();      // the previous tile's P.V must have drained before P is overwritten
-                        tmem_st32(p_tmem + (i >> 5) * 32, pk);
-                    }
-                    // the hand-off of a 64-key block trails its store by a few pairs, so that the MUFU keeps
-                    // running while the store drains (the last block has nothing left to overlap with)
-                    constexpr int kTrail = 6;
-                    if (((i & 31) == ((31 + kTrail) & 31) && i > 31) || i == kPairs - 1) {
-                        tmem_wait_st();
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) {
-                            if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, kPairs / 32 - 1));
-                            else mbar_arrive(bar_p_ready(q, (i >> 5) - 1));
+                };
+                const float m_new = fmaxf(m_used, mx_all);
+                if (j == 0) {
+                    m_used = m_new;
+                } else {
+                    const bool grow = (m_new - m_used) * sl2 > kRescaleThreshold;   // false for -inf - -inf (NaN)
+                    if (__any_sync(0xffffffffu, grow)) {
+                        wait_pv();
+                        const float alpha = grow ? ex2((m_used - m_new) * sl2) : 1.f;
+                        const uint64_t alpha2 = pack_f2(alpha, alpha);
+                        l_acc[0] = fmul2(l_acc[0], alpha2);
+                        l_acc[1] = fmul2(l_acc[1], alpha2);
+                        if (grow) m_used = m_new;
+#pragma unroll
+                        for (int c = 0; c < D / 16; ++c) {   // 16-column chunks: the scores stay in registers
+                            uint32_t o[16];
+                            tmem_ld16(o_tmem + 16 * c, o);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                            tmem_st16(o_tmem + 16 * c, o);
                         }
-                        trace_event(tr, q, j, i == kPairs - 1 ? 12 : 11);
                     }
                 }
-            };
-            if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
-            else exp_and_store(std::integral_constant<int, 0>{});
-            if constexpr (DBG == 5) {
-                const long long pt3 = clock64();
-                pt_wait += pt1 - pt0; pt_max += pt2 - pt1; pt_exp += pt3 - pt2;
+                const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
+                const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
+                SFA_TRACE(tr, t, q, 10);
+                // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
+                // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
+                auto exp_and_store = [&](auto poly_tag) {
+                    constexpr int kPoly = decltype(poly_tag)::value;
+                    constexpr int kPairs = kCols / 2;
+                    constexpr int kAhead = 3;            // pairs between the scale FFMA2 and its MUFUs
+                    uint64_t xq[kAhead];                 // scaled scores waiting for their exp2
+                    auto scale = [&](int i) {
+                        return ffma2_v(pack_f2(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), sl2_2, neg_m2);
+                    };
+#pragma unroll
+                    for (int i = 0; i < kAhead; ++i) xq[i] = scale(i);
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int i = 0; i < kPairs; ++i) {
+                        float x0, x1, p0, p1;
+                        unpack_f2(xq[i % kAhead], x0, x1);
+                        if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
+                        if ((i & 7) >= 8 - kPoly) {
+                            unpack_f2(exp2_poly2(x0, x1), p0, p1);
+                        } else {
+                            p0 = ex2_v(x0); p1 = ex2_v(x1);
+                        }
+                        l_acc[i & 1] = fadd2_v(l_acc[i & 1], pack_f2(p0, p1));
+                        pk[i & 31] = pack_pair<BF16>(p0, p1);
+                        if ((i & 31) == 31) {
+                            if (i == 31) wait_pv();      // the previous tile's P.V must have drained before P is overwritten
+                            tmem_st32(p_tmem + (i >> 5) * 32, pk);
+                        }
+                        // the hand-off of a 64-key block trails its store by a few pairs, so that the MUFU keeps
+                        // running while the store drains (the last block has nothing left to overlap with)
+                        constexpr int kTrail = 6;
+                        if (((i & 31) == ((31 + kTrail) & 31) && i > 31) || i == kPairs - 1) {
+                            tmem_wait_st();
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) {
+                                if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, kPairs / 32 - 1));
+                                else mbar_arrive(bar_p_ready(q, (i >> 5) - 1));
+                            }
+                            SFA_TRACE(tr, t, q, i == kPairs - 1 ? 12 : 11);
+                        }
+                    }
+                };
+                if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
+                else exp_and_store(std::integral_constant<int, 0>{});
             }
-        }
-        if (probe) {
-            g_fwd_probe[8 * q + 0] = pt_wait; g_fwd_probe[8 * q + 1] = pt_max; g_fwd_probe[8 * q + 2] = pt_exp;
-            g_fwd_probe[8 * q + 3] = n_q; g_fwd_probe[8 * q + 4] = pt_pv;
-        }
 
-        // ---- epilogue: O / l -> global, LSE
-        float l0, l1, l2, l3;
-        unpack_f2(l_acc[0], l0, l1);
-        unpack_f2(l_acc[1], l2, l3);
-        const float l_sum = (l0 + l1) + (l2 + l3);
-        const bool row_ok = row < p.seqlen_q;
-        const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
-        uint8_t* o_row = reinterpret_cast<uint8_t*>(p.o) +
-                         2 * ((int64_t)b * p.o_bs + (int64_t)row * p.o_rs + (int64_t)h * p.o_hs);
-        if constexpr (kFreeRun) {   // probe: nobody followed the phases of pv_done, walk through all of them
-            for (int j = 0; j + 1 < n_q && ok; ++j) ok = wait_barrier(bar_pv_done(q), j & 1, p.error_flag, 10);
-        }
-        if (n_q > 0 && ok) ok = wait_barrier(bar_pv_done(q), (n_q - 1) & 1, p.error_flag, 10);
-        tc_fence_after();
-        if (stamp) g_fwd_probe[26] = clock64();
-#pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
-            uint32_t o[32];
-            if (n_q > 0) {
-                tmem_ld32(o_tmem + 32 * c, o);
-                tmem_wait_ld();
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = 0u;
+            // ---- end of the item: O / l -> swizzled staging tile -> TMA store, LSE -> global
+            float l0, l1, l2, l3;
+            unpack_f2(l_acc[0], l0, l1);
+            unpack_f2(l_acc[1], l2, l3);
+            const float l_sum = (l0 + l1) + (l2 + l3);
+            const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
+            if (n_q > 0 && ok) {
+                ok = wait_barrier(bar_pv_done(q), (tiles + (uint32_t)n_q - 1u) & 1, p.error_flag, 10);
+                tc_fence_after();
+                if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)(n_q - 1) + 1u, n_q - 1);
             }
-            uint32_t packed[16];
+            SFA_STAMP(tr, 26);
+            if (it.m0 + q * kBlockM < p.seqlen_q) {      // uniform over the warpgroup
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-                packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
-            if (row_ok) {
-                uint4* dst = reinterpret_cast<uint4*>(o_row + 64 * c);
+                for (int c = 0; c < kSub; ++c) {
+                    uint32_t o[64];
+                    if (n_q > 0) {
+                        tmem_ld32(o_tmem + 64 * c, o);
+                        tmem_ld32(o_tmem + 64 * c + 32, o + 32);
+                        tmem_wait_ld();
+                    } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+                        for (int i = 0; i < 64; ++i) o[i] = 0u;
+                    }
+                    uint32_t packed[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
+                    // the staging tile is free once the previous TMA store has read it
+                    if (wg_leader) bulk_wait_read0();
+                    named_bar_sync(1 + q, 128);
+                    // row r of the tile is 128 B; its 16-byte chunk i sits at chunk i ^ (r & 7) (the 128-byte swizzle
+                    // of the tensor map): eight consecutive rows hit eight different bank groups
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        st_shared_v4(stage + row_in_tile * 128 + ((i ^ (row_in_tile & 7)) << 4), packed[4 * i],
+                                     packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + q, 128);
+                    if (wg_leader) {
+                        tma_store_4d(&o_map, stage, 64 * c, it.h, it.m0 + q * kBlockM, it.b);   // rows past seqlen_q are clipped
+                        bulk_commit();
+                    }
+                }
+                if (row < p.seqlen_q && p.lse) {
+                    const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
+                    p.lse[((int64_t)it.b * p.heads_q + it.h) * p.seqlen_q + row] = lse;
+                }
             }
+            SFA_STAMP(tr, 27);
+            tiles += (uint32_t)n_q;
+            ring += 2u * (uint32_t)it.n_max;
         }
-        if (row_ok && p.lse) {
-            const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
-            p.lse[((int64_t)b * p.heads_q + h) * p.seqlen_q + row] = lse;
-        }
-        if (stamp) g_fwd_probe[27] = clock64();
+        if (wg_leader) bulk_wait_all0();   // the stores read shared memory: it must outlive them
     } else {
-        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warps of the third warpgroup
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warp of the third warpgroup
     }
 
     // ---- teardown: every tcgen05 operation of this CTA has completed once the softmax warps are here
@@ -713,7 +801,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         tc_fence_after();
         tmem_dealloc(tmem_base, T::kCols);
     }
-    if (stamp) g_fwd_probe[28] = clock64();
+    SFA_STAMP(trace_cta && threadIdx.x == 0, 28);
 }
 
 // ------------------------------------------------------------------------------------------ host
@@ -753,73 +841,98 @@ int make_map(CUtensorMap* map, const void* base, int dtype, int head_dim, int he
     return SFA_OK;
 }
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int DBG>
-int launch_instance(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p,
-                    int batch, cudaStream_t stream) {
+struct FwdMaps {
+    alignas(64) CUtensorMap q, k, v, o;
+};
+
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, bool SOFTREL>
+int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, DBG>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, SOFTREL>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
         attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kAlloc);
     });
     SFA_CUDA_CHECK(attr_err);
-    const int m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
-    dim3 grid(m_blocks, p.heads_q, batch);
-    kern<<<grid, FwdRegs<NQ>::kThreads, L::kAlloc, stream>>>(qm, km, vm, p);
+    // Work-item order.  Items that run at the same time should share K/V in L2, and the heavy query blocks of
+    // the causal mask should go first (longest processing time first keeps the tail of the schedule short).  So:
+    // (batch, head) pairs in groups; inside a group, query blocks from the last to the first, heads innermost.  A
+    // group holds about two grids' worth of items: with 148 CTAs its K/V (~ 39 MB at head_dim 128) stays in L2.
+    p.m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
+    p.heads_total = batch * p.heads_q;
+    p.group_heads = (2 * sm_count + p.m_blocks - 1) / p.m_blocks;
+    if (p.group_heads < 1) p.group_heads = 1;
+    // keep the query heads of one kv head in one group (GQA)
+    p.group_heads = (p.group_heads + p.group - 1) / p.group * p.group;
+    const long long total = (long long)p.m_blocks * p.heads_total;
+    if (total > INT_MAX / 2) return fail(SFA_ERR_UNSUPPORTED, "fwd: more than 2^30 work items");
+    p.total_items = (int)total;
+    const int grid = (int)(total < sm_count ? total : sm_count);
+    if ((p.sched = fwd_sched_counters(stream)) == nullptr) return SFA_ERR_CUDA;
+    kern<<<grid, FwdRegs<NQ>::kThreads, L::kAlloc, stream>>>(m.q, m.k, m.v, m.o, p);
     SFA_CUDA_CHECK(cudaGetLastError());
     count_launch();
     return SFA_OK;
 }
 
 // Host launcher: the tile configuration per (head_dim, rows, dtype) - what the reference's Traits<> template
-// (src/traits.h:7-26) selects at compile time.  Ring depth: as many 128-key tiles as fit beside the Q tiles.
+// (src/traits.h:7-26) selects at compile time.  Ring depth: as many 128-key tiles as fit beside the Q tiles and
+// the O staging tiles.
 template <bool BF16>
-int launch_dtype(const CUtensorMap& qm, const CUtensorMap& km, const CUtensorMap& vm, const FwdParams& p, int batch,
-                 int head_dim, int nq, cudaStream_t stream) {
-    // Tuning / probe overrides (tools/fwd_time.py): SFA_FWD_POLY in {0,2,3}, SFA_FWD_DBG probes (bf16, head_dim 128
-    // and fp16, head_dim 64, two query tiles only), SFA_FWD_STAGES in {4,5} at head_dim 128.
-    static const int poly = [] { const char* e = getenv("SFA_FWD_POLY"); return e ? atoi(e) : -1; }();
-    static const int dbg = [] { const char* e = getenv("SFA_FWD_DBG"); return e ? atoi(e) : 0; }();
-    static const int stages = [] { const char* e = getenv("SFA_FWD_STAGES"); return e ? atoi(e) : 0; }();
-#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DBG_) \
-    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DBG_>(qm, km, vm, p, batch, stream)
+int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, int nq, int sm_count, cudaStream_t stream) {
+    const FwdTuning& tune = fwd_tuning();
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, SR_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_, SR_>(m, p, batch, sm_count, stream)
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 0);
-        if constexpr (BF16) {
-            if (dbg == 1) SFA_LAUNCH(128, 2, 4, 0, 1);
-            if (dbg == 2) SFA_LAUNCH(128, 2, 4, 0, 2);
-            if (dbg == 4) SFA_LAUNCH(128, 2, 4, 0, 4);
-            if (dbg == 5) SFA_LAUNCH(128, 2, 4, 0, 5);
-            if (dbg == 6) SFA_LAUNCH(128, 2, 4, 0, 6);
-            if (poly == 2) SFA_LAUNCH(128, 2, 4, 2, 0);
-            if (poly == 3) SFA_LAUNCH(128, 2, 4, 3, 0);
-            if (stages == 5) SFA_LAUNCH(128, 2, 5, 0, 0);
-        }
-        SFA_LAUNCH(128, 2, 4, 0, 0);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, false);
+#ifdef SFA_PROBES
+        if (tune.softrel == 1) SFA_LAUNCH(128, 2, 4, 0, true);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, false);
+#endif
+        SFA_LAUNCH(128, 2, 4, 0, false);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0);
-    if constexpr (!BF16) {
-        if (dbg == 5) SFA_LAUNCH(64, 2, 6, 0, 5);
-        if (poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0);
-        if (poly == 4) SFA_LAUNCH(64, 2, 6, 4, 0);
-    }
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, false);
+#ifdef SFA_PROBES
+    if (tune.softrel == 1) SFA_LAUNCH(64, 2, 6, 2, true);
+    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, false);
+#endif
     // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
     // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2, 0);
+    SFA_LAUNCH(64, 2, 6, 2, false);
 #undef SFA_LAUNCH
 }
 
 }  // namespace
+
+// Tuning overrides, read from the environment ONCE per process (test / tuning builds only act on most of them).
+const FwdTuning& fwd_tuning() {
+    static const FwdTuning t = [] {
+        FwdTuning v;
+        auto geti = [](const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; };
+        v.poly = geti("SFA_FWD_POLY", -1);
+        v.softrel = geti("SFA_FWD_SOFTREL", -1);
+        v.stagger = geti("SFA_FWD_STAGGER", -1);
+        v.nq = geti("SFA_FWD_NQ", 0);
+        v.v1 = geti("SFA_FWD_V1", 0);
+        return v;
+    }();
+    return t;
+}
 
 int fwd_error_flag_read(int* value) {
     SFA_CUDA_CHECK(cudaMemcpyFromSymbol(value, g_fwd_error, sizeof(int)));
     return SFA_OK;
 }
 int fwd_probe_read(unsigned long long* out, int n) {
-    if (n > 32 + 2048) n = 32 + 2048;
+#ifdef SFA_PROBES
+    if (n > 32 + 4096) n = 32 + 4096;
     SFA_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_fwd_probe, n * sizeof(unsigned long long)));
     return SFA_OK;
+#else
+    (void)out; (void)n;
+    return fail(SFA_ERR_UNSUPPORTED, "the prefill trace exists in the probe build only (libStarFlashAttention_probes.so)");
+#endif
 }
 int fwd_error_flag_clear() {
     const int zero = 0;
@@ -843,38 +956,34 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
     for (uintptr_t x : ptrs)
         if (x % 16) return fail(SFA_ERR_INVALID, "fwd: tensor base pointers must be 16-byte aligned");
     if (a.batch == 0 || a.seqlen_q == 0) return SFA_OK;
+    const FwdTuning& tune = fwd_tuning();
+    if (tune.v1) return launch_fwd_v1(a, stream);
     const DeviceInfo* dev = current_device();
     if (!dev) return SFA_ERR_NO_DEVICE;
 
-    alignas(64) CUtensorMap qm, km, vm;
+    FwdMaps m;
     int rc;
     // seqlen_k == 0 still needs valid maps; a one-row extent keeps the encoder happy and is never read.
     const int rows_k = a.seqlen_k > 0 ? a.seqlen_k : 1;
-    if ((rc = make_map(&qm, a.q, a.dtype, a.head_dim, a.heads_q, a.seqlen_q, a.batch, a.q_head_stride, a.q_row_stride, a.q_batch_stride))) return rc;
-    if ((rc = make_map(&km, a.k, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.k_head_stride, a.k_row_stride, a.k_batch_stride))) return rc;
-    if ((rc = make_map(&vm, a.v, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.v_head_stride, a.v_row_stride, a.v_batch_stride))) return rc;
+    if ((rc = make_map(&m.q, a.q, a.dtype, a.head_dim, a.heads_q, a.seqlen_q, a.batch, a.q_head_stride, a.q_row_stride, a.q_batch_stride))) return rc;
+    if ((rc = make_map(&m.k, a.k, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.k_head_stride, a.k_row_stride, a.k_batch_stride))) return rc;
+    if ((rc = make_map(&m.v, a.v, a.dtype, a.head_dim, a.heads_kv, rows_k, a.batch, a.v_head_stride, a.v_row_stride, a.v_batch_stride))) return rc;
+    if ((rc = make_map(&m.o, a.o, a.dtype, a.head_dim, a.heads_q, a.seqlen_q, a.batch, a.o_head_stride, a.o_row_stride, a.o_batch_stride))) return rc;
 
-    FwdParams p;
-    p.o = a.o; p.lse = a.lse;
-    p.o_bs = a.o_batch_stride; p.o_rs = a.o_row_stride; p.o_hs = a.o_head_stride;
+    FwdParams p = {};
+    p.lse = a.lse;
     p.seqlen_q = a.seqlen_q; p.seqlen_k = a.seqlen_k; p.heads_q = a.heads_q; p.group = a.heads_q / a.heads_kv;
-    p.causal = a.causal ? 1 : 0; p.is_bf16 = a.dtype == SFA_BF16;
+    p.causal = a.causal ? 1 : 0;
     const float scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
     p.scale_log2 = scale * kLog2e;
-    {
-        const char* e = getenv("SFA_FWD_STAGGER");
-        p.stagger_cycles = e ? atoi(e) : (a.head_dim == 64 ? kStaggerCycles64 : 0);
-        const char* lo = getenv("SFA_FWD_LOADORDER");
-        p.load_order = lo ? atoi(lo) : 1;
-    }
+    p.stagger_cycles = tune.stagger >= 0 ? tune.stagger : (a.head_dim == 64 ? kStaggerCycles64 : 0);
     void* flag_addr = nullptr;
     SFA_CUDA_CHECK(cudaGetSymbolAddress(&flag_addr, g_fwd_error));
     p.error_flag = reinterpret_cast<int*>(flag_addr);
 
-    static int forced_nq = [] { const char* e = getenv("SFA_FWD_NQ"); return e ? atoi(e) : 0; }();
-    const int nq = forced_nq == 1 || forced_nq == 2 ? forced_nq : (a.seqlen_q > kBlockM ? 2 : 1);
-    return a.dtype == SFA_BF16 ? launch_dtype<true>(qm, km, vm, p, a.batch, a.head_dim, nq, stream)
-                               : launch_dtype<false>(qm, km, vm, p, a.batch, a.head_dim, nq, stream);
+    const int nq = tune.nq == 1 || tune.nq == 2 ? tune.nq : (a.seqlen_q > kBlockM ? 2 : 1);
+    return a.dtype == SFA_BF16 ? launch_dtype<true>(m, p, a.batch, a.head_dim, nq, dev->sm_count, stream)
+                               : launch_dtype<false>(m, p, a.batch, a.head_dim, nq, dev->sm_count, stream);
 }
 
 }  // namespace sfa

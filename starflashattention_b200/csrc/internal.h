@@ -24,7 +24,8 @@ struct DeviceInfo {
 // Cached per-device properties; returns nullptr (and sets the error) when no sm_100 device is current.
 const DeviceInfo* current_device();
 
-// Per-device grow-only scratch (never shrinks; grown only outside stream capture).
+// Grow-only scratch of one (device, stream); outgrown buffers are retired, never freed under a caller's feet
+// (freed by sfa_release_workspaces only); grown only outside stream capture.
 void* get_workspace(size_t bytes, cudaStream_t stream);
 
 #define SFA_CUDA_CHECK(expr)                                                                  \
@@ -97,6 +98,19 @@ int launch_fill(void* arr, float value, int64_t n, int dtype, cudaStream_t strea
 
 // ------------------------------------------------------------------ prefill (fwd_sm100.cu)
 int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream);
+int launch_fwd_v1(const sfa_fwd_args& a, cudaStream_t stream);   // round-1 kernel (one CTA per query block), A/B only
+int fwd_error_flag_read_v1(int* value);
+int fwd_error_flag_clear_v1();
+// Tuning overrides of the prefill launcher, read from the environment once per process.
+struct FwdTuning {
+    int poly = -1, softrel = -1, stagger = -1, nq = 0, v1 = 0;
+};
+const FwdTuning& fwd_tuning();
+// Two zeroed ints (next-item counter, CTAs done) for one launch of the persistent prefill kernel; the kernel
+// leaves them zero again.  Slots rotate per launch, launches under stream capture get slots of their own.
+int* fwd_sched_counters(cudaStream_t stream);
+// Rezeroes every slot (after a watchdog abort left counters behind).
+int fwd_sched_reset();
 // Pipeline watchdog of the prefill kernel: non-zero after an mbarrier wait timed out.
 int fwd_error_flag_read(int* value);
 int fwd_error_flag_clear();

@@ -142,9 +142,18 @@ def _spot_check(q, k, v, o, lse, causal, rows, heads, dtype):
                    f"b{b} h{h} r{r}", mag=mag)
 
 
+def _sample_rows(S, seed, n_random):
+    """Fixed rows around every tile / block boundary the kernel has (128-row query tiles, 256-row CTA blocks:
+    first and last rows, the SECOND query tile of the first, a middle and the last block) plus seeded random rows."""
+    g = torch.Generator().manual_seed(seed)
+    fixed = [0, 127, 128, 255, 256, S // 2 - 1, S // 2, S // 2 + 129, S - 256, S - 256 + 5, S - 128, S - 128 + 100, S - 1]
+    rnd = torch.randint(0, S, (n_random,), generator=g).tolist()
+    return sorted(set(fixed + rnd))
+
+
 def test_fwd_full_c3_shape_spot_check():
-    """BASELINE config 3 at full size (causal bf16 B=8 H=32 N=8192 d=128): sampled rows of sampled heads
-    against the oracle, everything for finiteness."""
+    """BASELINE config 3 at full size (causal bf16 B=8 H=32 N=8192 d=128): 25 rows (tile boundaries + a seeded
+    random dozen) of 8 (batch, head) pairs against the oracle, O and LSE; everything for finiteness."""
     import starflashattention_b200 as sfa
     dtype = torch.bfloat16
     B, S, H, D = 8, 8192, 32, 128
@@ -152,8 +161,101 @@ def test_fwd_full_c3_shape_spot_check():
     q, k, v = (torch.randn((B, S, H, D), generator=g, device="cuda", dtype=torch.float32).to(dtype) for _ in range(3))
     o, lse = sfa.fwd(q, k, v, causal=True)
     torch.cuda.synchronize()
+    assert sfa.fwd_watchdog() == 0
     assert torch.isfinite(o).all() and torch.isfinite(lse).all()
-    _spot_check(q, k, v, o, lse, True, [0, 127, 128, 4095, 4096, 8191], [(0, 0), (7, 31), (3, 17)], dtype)
+    rows = _sample_rows(S, 33, 12)
+    assert len(rows) >= 24
+    heads = [(0, 0), (7, 31), (3, 17), (1, 5), (2, 30), (4, 11), (5, 24), (6, 8)]
+    _spot_check(q, k, v, o, lse, True, rows, heads, dtype)
+
+
+def test_fwd_full_c5_shape_spot_check():
+    """BASELINE config 5 at full size on one GPU (causal bf16 B=1 H=32 N=65536 d=128: 256 query blocks per head, up
+    to 512 key tiles per query tile, 256 wraps of the K/V ring per item, TMA row coordinates up to 65408): 25 rows
+    (including rows of the SECOND query tile of late blocks: 65408+100, 65535, 32768+129) of 5 heads against the
+    oracle, O and LSE; everything for finiteness; watchdog clean."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    B, S, H, D = 1, 65536, 32, 128
+    g = torch.Generator(device="cuda").manual_seed(5)
+    q, k, v = (torch.randn((B, S, H, D), generator=g, device="cuda", dtype=torch.float32).to(dtype) for _ in range(3))
+    o, lse = sfa.fwd(q, k, v, causal=True)
+    torch.cuda.synchronize()
+    assert sfa.fwd_watchdog() == 0
+    assert torch.isfinite(o).all() and torch.isfinite(lse).all()
+    rows = _sample_rows(S, 55, 12)
+    assert len(rows) >= 24 and 65535 in rows and 65408 + 100 in rows and 32768 + 129 in rows
+    _spot_check(q, k, v, o, lse, True, rows, [(0, 0), (0, 7), (0, 16), (0, 21), (0, 31)], dtype)
+
+
+def test_fwd_many_items_per_cta_mixed_lengths():
+    """The persistent CTAs walk through many work items each (heavy-first order, atomic hand-out): 2400 items of 1 to
+    6 key-tile pairs on 148 CTAs, GQA; every (batch, head) is checked in full against the oracle on a second,
+    smaller problem, and the large one through the causal prefix property against itself."""
+    import starflashattention_b200 as sfa
+    dtype = torch.bfloat16
+    q = _rand((3, 1300, 8, 128), dtype, 41)
+    k = _rand((3, 1300, 2, 128), dtype, 42)
+    v = _rand((3, 1300, 2, 128), dtype, 43)
+    o_ref, lse_ref, mag = _oracle(q, k, v, causal=True)
+    o, lse = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=True)
+    _check(o, lse, o_ref, lse_ref, dtype, "many items", mag=mag)
+    # twice in a row on the same stream: the schedule counters must come back to zero by themselves
+    o2, lse2 = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=True)
+    assert torch.equal(o2, o) and torch.equal(lse2, lse)
+    g = torch.Generator(device="cuda").manual_seed(44)
+    qb, kb, vb = (torch.randn((50, 1536, 8, 128), generator=g, device="cuda", dtype=torch.float32).to(dtype) for _ in range(3))
+    ob, lb = sfa.fwd(qb, kb, vb, causal=True)
+    n = 640
+    op, lp = sfa.fwd(qb[:, :n], kb[:, :n], vb[:, :n], causal=True)
+    assert float((ob[:, :n].float() - op.float()).abs().max()) <= 2e-3 + 2.0 ** -8 * 4.0
+    assert float((lb[:, :, :n] - lp).abs().max()) <= 1e-4
+
+
+def test_fwd_graph_capture_and_two_streams():
+    """The prefill call is capturable (its schedule counters belong to the captured launch) and two streams may run it
+    at the same time (every launch has counters of its own)."""
+    import starflashattention_b200 as sfa
+    dtype = torch.float16
+    q, k, v = (_rand((2, 512, 4, 128), dtype, s).cuda() for s in (51, 52, 53))
+    o_ref, lse_ref = sfa.fwd(q, k, v, causal=True)
+    torch.cuda.synchronize()
+    out = torch.empty_like(q)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        sfa.fwd(q, k, v, causal=True, out=out, return_lse=False)
+    for _ in range(3):
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, o_ref)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    outs = []
+    for s in (s1, s2) * 4:
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            outs.append(sfa.fwd(q, k, v, causal=True)[0])
+    torch.cuda.synchronize()
+    assert all(torch.equal(x, o_ref) for x in outs)
+
+
+def test_fwd_bf16_noise_floor():
+    """the FlashAttention convention - the kernel's error against an fp64 evaluation must not exceed
+    twice the error of a NAIVE evaluation in the data type (bf16 matmuls and softmax by torch on the GPU, the
+    same formula as examples/python/testFlashDecoder.py:84-92) against the same fp64 result.  Printed with -s."""
+    import starflashattention_b200 as sfa
+    for dtype in (torch.bfloat16, torch.float16):
+        q, k, v = (_rand((1, 1024, 4, 128), dtype, s) for s in (61, 62, 63))
+        o64, _ = naive.attention_fwd(q, k, v, causal=True, acc_dtype=torch.float64)
+        o, _ = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=True)
+        qd, kd, vd = (t.cuda().transpose(1, 2) for t in (q, k, v))           # (B, H, S, D)
+        s = torch.matmul(qd, kd.transpose(-1, -2)) / (128 ** 0.5)
+        s = s.masked_fill(torch.ones(1024, 1024, device="cuda", dtype=torch.bool).triu(1), float("-inf"))
+        o_naive = torch.matmul(torch.softmax(s, dim=-1), vd).transpose(1, 2)
+        err_kernel = float((o.double().cpu() - o64).abs().max())
+        err_naive = float((o_naive.double().cpu() - o64).abs().max())
+        print(f"[noise floor] {dtype}: kernel max |O - O_fp64| = {err_kernel:.3e}, naive {dtype} = {err_naive:.3e}")
+        assert err_kernel <= 2.0 * err_naive + 1e-5, (dtype, err_kernel, err_naive)
 
 
 def test_fwd_full_c2_shape_spot_check():

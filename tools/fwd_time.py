@@ -1,5 +1,6 @@
-"""Device-resident timing of the prefill kernel for one configuration (env overrides SFA_FWD_POLY / SFA_FWD_DBG
-are read by the library at first launch, so every variant runs in its own process).
+"""Device-resident timing of the prefill kernel for one configuration (the SFA_FWD_* overrides are read by the
+library once per process, so every variant runs in its own process; most act in the probe build only:
+SFA_PROBES_LIB=1 after `python starflashattention_b200/build.py --probes`).
 
     python tools/fwd_time.py c3|c2|c5 [iters]
 """
@@ -64,19 +65,8 @@ def main():
                f"{statistics.median(half):.0f} MHz min {min(sm)} max {max(sm)}, power max {max(pw):.0f} W")
     except Exception as e:  # noqa: BLE001
         clk = f" | clock sampling failed: {e!r}"
-    if os.environ.get("SFA_FWD_DBG") in ("4", "5"):
-        import ctypes
-        from starflashattention_b200 import _capi
-        buf = (ctypes.c_uint64 * 32)()
-        _capi.lib.sfa_fwd_probe_read(buf, 32)
-        v_ = list(buf)
-        for qq in (0, 1):
-            n = max(1, v_[8 * qq + 3])
-            print(f"[probe] softmax q{qq}: tiles {n}  per tile: wait S {v_[8*qq]/n:.0f}  ld+max {v_[8*qq+1]/n:.0f}  "
-                  f"exp+store {v_[8*qq+2]/n:.0f} (of which wait PV {v_[8*qq+4]/n:.0f}) cycles")
-        n = max(1, v_[20])
-        print(f"[probe] mma warp: iters {n}  per iter: wait P {v_[16]/n:.0f}  wait S-free {v_[17]/n:.0f}  wait KV {v_[18]/n:.0f}  total {v_[19]/n:.0f} cycles")
-    print(f"[fwd_time] {name} POLY={os.environ.get('SFA_FWD_POLY','-')} DBG={os.environ.get('SFA_FWD_DBG','-')} STAGES={os.environ.get('SFA_FWD_STAGES','-')} "
+    tag = " ".join(f"{k[8:]}={v}" for k, v in sorted(os.environ.items()) if k.startswith("SFA_FWD_")) or "product"
+    print(f"[fwd_time] {name} [{tag}{' probes-lib' if os.environ.get('SFA_PROBES_LIB') == '1' else ''}] "
           f"median {ms:.3f} ms  min {min(ts):.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s (median)  watchdog={wd}{clk}", flush=True)
 
 
