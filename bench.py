@@ -13,7 +13,8 @@ Prints ONE JSON line.  A step is one pass of the hot path over one batch of synt
 ``value`` is measured with the inputs resident in HBM (CUDA events on the launching stream, max over
 ranks); ``e2e`` is the same metric through the public API with pinned host buffers, host<->device copies
 inside the timed region.  Multi-GPU: one process per GPU (torchrun); the (batch x head) units are
-independent, so every rank runs the full per-GPU workload with no collective in the timed path (weak scaling).
+independent, so the units of ONE problem are cut over the ranks with no collective in the timed path (strong scaling:
+C3 at N=8 is one batch entry per GPU, C5 four heads per GPU).
 ``--impl reference`` times the reference's own CPU path (the naive softmax(QK^T/sqrt d)V of its Python
 example, restated in oracle/naive.py) on the host cores, on a bounded sample of the same workload.
 """
@@ -59,20 +60,13 @@ def algorithmic_bytes(name):
     return 2.0 * B * S * Hkv * D * 2                                          # K and V once
 
 
-def load_traffic(name):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/r1d_traffic.json)."""
-    try:
-        return float(json.load(open(os.path.join(ROOT, "profiles", "r1d_traffic.json")))[name]["bytes_per_launch"])
-    except Exception:  # noqa: BLE001
-        return None
-
-
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
         p = json.load(open(path))
-        return {"hbm": float(p["hbm_gbs"]), "tensor": float(p["bf16_tflops"]), "source": "measured"}
-    return {"hbm": 6650.0, "tensor": 1590.0, "source": "fallback"}
+        return {"hbm": float(p["hbm_gbs"]), "tensor": float(p["bf16_tflops"]),
+                "tensor_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), "source": "MEASURED_PEAKS.json"}
+    return {"hbm": 6650.0, "tensor": 1590.0, "tensor_sustained": 1590.0, "source": "fallback (B200_PROFILING.md)"}
 
 
 class ClockSampler:
@@ -162,13 +156,14 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
-def make_inputs(name, device, seed):
-    """Synthetic N(0,1) inputs: drawn on the device, mirrored into pinned host buffers for the e2e leg."""
-    kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
+def make_inputs(shape, device, seed):
+    """Synthetic N(0,1) inputs of a (kind, dtype, B, Hq, Hkv, S, D, causal) problem: drawn on the device, mirrored into
+    pinned host buffers for the e2e leg."""
+    kind, dtype, B, Hq, Hkv, S, D, causal = shape
     g = torch.Generator(device=device).manual_seed(seed)
 
-    def rnd(shape):
-        t = torch.empty(shape, dtype=dtype, device=device)
+    def rnd(shp):
+        t = torch.empty(shp, dtype=dtype, device=device)
         flat = t.view(-1)
         step = 1 << 26
         for i in range(0, flat.numel(), step):
@@ -188,6 +183,125 @@ def make_inputs(name, device, seed):
     return host, dev_t
 
 
+def workload_config(name, world):
+    """The `config` object of the JSON line: the same for both arms (it names the workload, not the implementation)."""
+    kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
+    per = B * Hkv // max(1, world)
+    return {"workload": f"{name}: {kind} B={B} Hq={Hq} Hkv={Hkv} N={S} d={D} causal={causal}",
+            "l2": "inputs larger than L2 (no flush)" if (name != "c2" and world < 8) else
+                  "per-rank inputs may fit L2 between steps (no flush)",
+            "parallelism": f"one problem per step; its {B * Hkv} (batch x kv-head) units cut over {world} rank(s), "
+                           f"{per} per rank, no collective in the timed path"}
+
+
+def local_shape(name, world, rank):
+    """This rank's share of a workload: the (batch x kv-head) units are cut into contiguous slices
+    (starflashattention_b200.multi_gpu.partition); a slice is either whole batch entries or a
+    range of the kv-heads of one entry.  Returns the local problem shape and its share of the work."""
+    from starflashattention_b200.multi_gpu import partition
+    kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
+    mine = partition(B * Hkv, world, rank)
+    n = len(mine)
+    g = Hq // Hkv
+    if n % Hkv == 0 and mine.start % Hkv == 0:
+        b_loc, hkv_loc = n // Hkv, Hkv
+    elif n > 0 and mine.start // Hkv == (mine.stop - 1) // Hkv:
+        b_loc, hkv_loc = 1, n
+    else:
+        raise SystemExit(f"{name}: {B * Hkv} units do not cut into whole entries or head ranges over {world} ranks")
+    return (kind, dtype, b_loc, hkv_loc * g, hkv_loc, S, D, causal), n / (B * Hkv)
+
+
+def step_fn(sfa, shape, d, out):
+    kind, dtype, B, Hq, Hkv, S, D, causal = shape
+    if kind == "fwd":
+        return lambda: sfa.fwd(d["q"], d["k"], d["v"], causal=causal, out=out, return_lse=True)
+    return lambda: sfa.decode(d["q"], d["k"], d["v"], d["seqlens"], out=out)
+
+
+def timed(fn, steps, dev, world, dist, flush=None):
+    """K calls between two CUDA events on the current stream (after a barrier + synchronise), max over ranks."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if flush is None:
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    else:           # L2 flushed before every call: one event pair per call
+        ms = 0.0
+        for _ in range(steps):
+            flush.zero_()
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+    if world > 1:
+        dist.barrier()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), ms
+
+
+def copy_floor(host, out_host, lse_host, dev, world, dist, reps=3):
+    """The box's own ceiling for the e2e leg: plain cudaMemcpyAsync of the step's input bytes (pinned host -> device)
+    on one stream and of its output bytes (device -> pinned host) on another, at the same time, on every rank at once;
+    no kernel.  Best of `reps`, max over ranks."""
+    s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    d_in = {k_: torch.empty(v_.shape, dtype=v_.dtype, device=dev) for k_, v_ in host.items()}
+    d_out, d_lse = torch.empty(out_host.shape, dtype=out_host.dtype, device=dev), torch.empty(lse_host.shape, dtype=torch.float32, device=dev)
+    best = float("inf")
+    for _ in range(reps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        cur = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        s_in.wait_event(e0); s_out.wait_event(e0)
+        with torch.cuda.stream(s_in):
+            for k_ in host:
+                d_in[k_].copy_(host[k_], non_blocking=True)
+        with torch.cuda.stream(s_out):
+            out_host.copy_(d_out, non_blocking=True)
+            lse_host.copy_(d_lse, non_blocking=True)
+        cur.wait_stream(s_in); cur.wait_stream(s_out)
+        e1.record(cur)
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    t = torch.tensor([best], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    del d_in, d_out, d_lse
+    return float(t.item())
+
+
+def source_hash(*names):
+    import hashlib
+    h = hashlib.sha256()
+    for n in names:
+        with open(os.path.join(ROOT, "starflashattention_b200", "csrc", n), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def load_traffic(name):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/r2_traffic.json).  The entry names the kernel and carries a hash of the kernel's source file; it is
+    printed only while that hash still matches the source this run was built from."""
+    try:
+        e = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))[name]
+        if e.get("source_hash") != source_hash(*e["sources"]):
+            return None
+        return {"bytes_per_launch": float(e["bytes_per_launch"]), "kernel": e["kernel"], "capture": e.get("capture")}
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def run_ours(args):
     import starflashattention_b200 as sfa
     import torch.distributed as dist
@@ -201,178 +315,169 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    peaks = load_peaks()
 
     name = args.workload
     kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
     units = workload_units(name)
-    # c5 (BASELINE config 5) is ONE long-context problem whose heads are sharded over the ranks (strong scaling,
-    # starflashattention_b200.multi_gpu.partition); every other workload runs in full on every rank (weak scaling).
-    strong = name == "c5" and world > 1
-    Hq_all, Hkv_all = Hq, Hkv
-    if strong:
-        my_heads = sfa.partition(Hkv, world, rank)
-        frac = len(my_heads) / Hkv
-        Hq, Hkv = Hq // Hkv * len(my_heads), len(my_heads)
-        WORKLOADS[name] = (kind, dtype, B, Hq, Hkv, S, D, causal)
-        units = dict(units, amount=units["amount"] * frac)
-    host, d = make_inputs(name, dev, seed=100 + rank)
-    if kind == "fwd":
-        out = torch.empty((B, S, Hq, D), dtype=dtype, device=dev)
-
-        def step():
-            return sfa.fwd(d["q"], d["k"], d["v"], causal=causal, out=out)
-    else:
-        out = torch.empty((B, Hq, D), dtype=dtype, device=dev)
-
-        def step():
-            return sfa.decode(d["q"], d["k"], d["v"], d["seqlens"], out=out)
-    torch.cuda.synchronize()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    # ONE problem per step, its (batch x kv-head) units cut over the ranks with no collective in the timed path
+    # (strong scaling): C3 at N=8 is 32 units = one batch entry per GPU, C5 four heads per GPU, C4 one sequence per GPU.
+    shape, share = local_shape(name, world, rank)
+    _, _, Bl, Hql, Hkvl, _, _, _ = shape
+    host, d = make_inputs(shape, dev, seed=100 + rank)
+    out = torch.empty((Bl, S, Hql, D) if kind == "fwd" else (Bl, Hql, D), dtype=dtype, device=dev)
+    step = step_fn(sfa, shape, d, out)
 
     # ---- device-resident timing
     for _ in range(args.warmup):
         step()
-    barrier()
+    torch.cuda.synchronize()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     launches0 = sfa.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    barrier()
+    ms_max, ms_own = timed(step, args.steps, dev, world, dist)
     launches = sfa.launch_count() - launches0
-    ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     if kind == "fwd":
         wd = sfa.fwd_watchdog()
         if wd:
             raise SystemExit(f"prefill pipeline watchdog fired (code {wd}); the timing is void")
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
     ms_per_step = ms_max / args.steps
-    total_amount = units["amount"]
-    if world > 1:
-        ta = torch.tensor([units["amount"]], dtype=torch.float64, device=dev)
-        dist.all_reduce(ta, op=dist.ReduceOp.SUM)          # units all ranks processed (outside the timed region)
-        total_amount = float(ta.item())
-    value = total_amount / (ms_per_step / 1e3)
+    value = units["amount"] / (ms_per_step / 1e3)          # the whole problem over the slowest rank's time
 
-    # ---- end to end through the public host-buffer API (fwd_host / decode_host): pinned host inputs -> H2D ->
-    # kernel -> D2H of the result, every step; the API cuts the independent (batch x head) units into chunks so
-    # that upload, kernel and download overlap on three streams.
+    # ---- end to end through the public host-buffer API (sfa_fwd_host / sfa_decode_host in the C ABI): pinned host
+    # inputs -> H2D -> kernel -> D2H of the result, every step; the library cuts the call into pieces so that upload,
+    # kernel and download overlap on three streams.
     out_host = torch.empty(out.shape, dtype=dtype, pin_memory=True)
-    lse_shape = (B, Hq, S) if kind == "fwd" else (B, Hq)
-    lse_host = torch.empty(lse_shape, dtype=torch.float32, pin_memory=True)
+    lse_host = torch.empty((Bl, Hql, S) if kind == "fwd" else (Bl, Hql), dtype=torch.float32, pin_memory=True)
     seq_host = host.get("seqlens")
-    e2e_steps = max(2, min(args.steps, 5))
 
     def e2e_step():
         if kind == "fwd":
             sfa.fwd_host(host["q"], host["k"], host["v"], causal=causal, out=out_host, lse=lse_host, device=dev)
         else:
             sfa.decode_host(host["q"], host["k"], host["v"], seq_host, out=out_host, lse=lse_host, device=dev)
-    e2e_step()
-    barrier()
-    launches_e2e0 = sfa.launch_count()
-    e0.record()
-    for _ in range(e2e_steps):
+    for _ in range(2):
         e2e_step()
-    e1.record()
-    barrier()
-    launches_e2e = (sfa.launch_count() - launches_e2e0) // e2e_steps
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item()) / e2e_steps
+    launches_e2e0 = sfa.launch_count()
+    e2e_max, _ = timed(e2e_step, args.steps, dev, world, dist)
+    launches_e2e = (sfa.launch_count() - launches_e2e0) // args.steps
+    e2e_ms = e2e_max / args.steps
     h2d = sum(v.numel() * v.element_size() for v in host.values())
     d2h = out_host.numel() * out_host.element_size() + lse_host.numel() * lse_host.element_size()
+    floor_ms = copy_floor(host, out_host, lse_host, dev, world, dist)
 
+    # ---- a seconds-long back-to-back loop of the same step (what the clock settles at under the power cap)
+    sustained = None
+    if kind == "fwd" and world == 1 and not args.no_sustained:
+        n_sus = max(args.steps, int(2500.0 / max(ms_per_step, 1e-3)))
+        s2 = ClockSampler(local_rank)
+        s2.start()
+        sus_max, _ = timed(step, n_sus, dev, world, dist)
+        c2 = s2.stop()
+        rate = units["amount"] / (sus_max / n_sus / 1e3)
+        sustained = {"value": rate, "unit": units["unit"], "steps": n_sus, "seconds": sus_max / 1e3, "ms_per_step": sus_max / n_sus,
+                     "peak": peaks["tensor_sustained"], "frac": rate / peaks["tensor_sustained"], "clocks": c2,
+                     "peak_source": peaks["source"] + " sustained (bf16_tflops_sustained)"}
+
+    sec = None
+    if not args.no_secondary:
+        sec = secondary(sfa, name, dev, peaks, world, rank, dist)
     if rank == 0:
-        peaks = load_peaks()
         peak = peaks[units["bound"]]
-        per_gpu = units["amount"] / (ms / args.steps / 1e3)      # rank 0's own kernel rate
+        per_gpu = units["amount"] * share / (ms_own / args.steps / 1e3)      # rank 0's own kernel rate on its share
         line = {
             "metric": units["metric"], "value": value, "unit": units["unit"], "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong" if strong else "weak",
+            "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16" if dtype == torch.bfloat16 else "fp16", "data": "synthetic",
-            "config": {"workload": f"{name}: {kind} B={B} Hq={Hq_all} Hkv={Hkv_all} N={S} d={D} causal={causal}",
-                       "l2": "inputs larger than L2 (no flush)" if name != "c2" else "inputs 101 MB, L2-resident between steps",
-                       "parallelism": (f"heads of one problem sharded over {world} rank(s), no collective" if strong else
-                                       f"batch x heads units, {world} independent rank(s) each with the full per-GPU workload, no collective")},
-            "e2e": {"value": total_amount / (e2e_ms / 1e3), "unit": units["unit"],
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
-                    "api": "fwd_host" if kind == "fwd" else "decode_host", "launches_per_step": int(launches_e2e)},
+            "config": workload_config(name, world),
+            "e2e": {"value": units["amount"] / (e2e_ms / 1e3), "unit": units["unit"],
+                    "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world, "ms_per_step": e2e_ms,
+                    "api": "sfa_fwd_host (C ABI) via fwd_host" if kind == "fwd" else "sfa_decode_host (C ABI) via decode_host",
+                    "launches_per_step": int(launches_e2e), "steps": args.steps,
+                    "copy_floor_ms": floor_ms, "over_copy_floor": e2e_ms / floor_ms if floor_ms > 0 else None,
+                    "copy_floor_note": "plain pinned cudaMemcpyAsync of the same bytes, H2D and D2H streams at once, all ranks "
+                                       "at once, no kernel; per-rank bytes = the totals / n_gpus"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": units["bound"], "achieved": per_gpu, "peak": peak,
                          "unit": "TFLOP/s" if units["bound"] == "tensor" else "GB/s", "frac": per_gpu / peak,
-                         "traffic": load_traffic(name) if not strong else None, "traffic_unit": "bytes per launch (ncu)",
-                         "algorithmic_bytes": algorithmic_bytes(name), "peak_source": peaks["source"] + (" burst" if units["bound"] == "tensor" else "")},
+                         "traffic": None, "algorithmic_bytes": algorithmic_bytes(name) * share,
+                         "peak_source": peaks["source"] + (" burst (bf16_tflops)" if units["bound"] == "tensor" else " (hbm_gbs)"),
+                         "per": "rank 0's share of the problem over rank 0's own event time"},
         }
+        tr = load_traffic(name) if world == 1 else None
+        if tr:
+            line["roofline"]["traffic"] = tr["bytes_per_launch"]
+            line["roofline"]["traffic_source"] = {"kernel": tr["kernel"], "capture": tr["capture"],
+                                                  "note": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum per launch; "
+                                                          "printed only while the kernel source hash matches the capture's"}
         if units["bound"] == "hbm":
             # MEASURED_PEAKS.json's hbm_gbs is a read + write copy; a read-only stream has no bus turnarounds and can
             # sit a few percent above it, so frac may exceed 1
             line["roofline"]["peak_note"] = "peak = measured read+write copy bandwidth; the decode stream is read-only"
+        if sustained:
+            line["sustained"] = sustained
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(name, budget_s=args.cpu_budget)
-        if world == 1 and not args.no_secondary:
-            line["secondary"] = secondary(sfa, name, dev, peaks)
+        if sec:
+            line["secondary"] = sec
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def secondary(sfa, primary, dev, peaks):
-    """Short device-resident timings of the other BASELINE configs (explanatory, not the headline)."""
+def secondary(sfa, primary, dev, peaks, world, rank, dist):
+    """Device-resident timings of the other BASELINE configs, sharded like the primary (explanatory, not the
+    headline): each with its own roofline object and clock samples.  At N=1 also the section-8(d) decode variants."""
     res = {}
-    for name in ("c4", "c2"):
+    cases = [("c4", None), ("c5", None)] + ([("c2", None), ("c4_b1_flushed", ("decode", torch.bfloat16, 1, 32, 8, 32768, 128, False)),
+                                             ("c4_b32", ("decode", torch.bfloat16, 32, 32, 8, 32768, 128, False))] if world == 1 else [])
+    for name, custom in cases:
         if name == primary:
             continue
         try:
-            kind, dtype, B, Hq, Hkv, S, D, causal = WORKLOADS[name]
-            units = workload_units(name)
-            g = torch.Generator(device=dev).manual_seed(7)
-            mk = lambda shape: torch.randn(shape, generator=g, device=dev, dtype=torch.float32).to(dtype)
+            if custom is None:
+                shape, share = local_shape(name, world, rank)
+                full = WORKLOADS[name]
+            else:
+                shape, share, full = custom, 1.0, custom
+            kind, dtype, B, Hq, Hkv, S, D, causal = full
+            amount = (4.0 * B * Hq * S * S * D * (0.5 if causal else 1.0) / 1e12) if kind == "fwd" else (2.0 * B * S * Hkv * D * 2 / 1e9)
+            bound = "tensor" if kind == "fwd" else "hbm"
+            _, _, Bl, Hql, Hkvl, _, _, _ = shape
+            g = torch.Generator(device=dev).manual_seed(7 + rank)
+            mk = lambda shp: torch.randn(shp, generator=g, device=dev, dtype=torch.float32).to(dtype)
             if kind == "fwd":
-                q, k, v = mk((B, S, Hq, D)), mk((B, S, Hkv, D)), mk((B, S, Hkv, D))
+                q, k, v = mk((Bl, S, Hql, D)), mk((Bl, S, Hkvl, D)), mk((Bl, S, Hkvl, D))
                 fn = lambda: sfa.fwd(q, k, v, causal=causal)
             else:
-                q, k, v = mk((B, Hq, D)), mk((B, S, Hkv, D)), mk((B, S, Hkv, D))
-                sl = torch.full((B,), S, dtype=torch.int32, device=dev)
+                q, k, v = mk((Bl, Hql, D)), mk((Bl, S, Hkvl, D)), mk((Bl, S, Hkvl, D))
+                sl = torch.full((Bl,), S, dtype=torch.int32, device=dev)
                 fn = lambda: sfa.decode(q, k, v, sl)
-            flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if name == "c2" else None
+            # inputs that fit the 126 MB L2 are flushed out before every call
+            in_bytes = 2.0 * (q.numel() + k.numel() + v.numel())
+            flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if in_bytes < 400e6 else None
             for _ in range(3):
                 fn()
-            torch.cuda.synchronize()
-            times = []
-            # flushed workloads: one call per event pair behind the flush kernel (which also hides the host's
-            # enqueue time); the others: 10 back-to-back calls per event pair, as the primary line is timed
-            inner = 1 if flush is not None else 10
-            for _ in range(10 if flush is not None else 5):
-                if flush is not None:
-                    flush.zero_()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                for _ in range(inner):
-                    fn()
-                e1.record()
-                torch.cuda.synchronize()
-                times.append(e0.elapsed_time(e1) / inner)
-            ms = statistics.median(times)
-            rate = units["amount"] / (ms / 1e3)
-            res[name] = {"metric": units["metric"], "value": rate, "unit": units["unit"], "ms": ms,
-                         "frac_of_measured_peak": rate / peaks[units["bound"]],
-                         "l2": "flushed between iterations" if flush is not None else "inputs larger than L2"}
+            n = 20 if flush is not None else (5 if name == "c5" and world == 1 else 20)
+            smp = ClockSampler(dev.index)
+            if rank == 0:
+                smp.start()
+            ms_max, ms_own = timed(fn, n, dev, world, dist, flush=flush)
+            clk = smp.stop() if rank == 0 else None
+            ms = ms_max / n
+            rate = amount / (ms / 1e3)
+            own = amount * share / (ms_own / n / 1e3)
+            res[name] = {"metric": "attn_fwd_tflops" if kind == "fwd" else "decode_kv_gbs", "value": rate,
+                         "unit": "TFLOP/s" if kind == "fwd" else "GB/s", "ms": ms, "steps": n,
+                         "config": f"{kind} B={B} Hq={Hq} Hkv={Hkv} N={S} d={D} causal={causal}; {Bl} x {Hkvl} (batch x kv-head) per rank",
+                         "l2": "flushed (256 MB written) before every call" if flush is not None else "inputs larger than L2",
+                         "roofline": {"bound": bound, "achieved": own, "peak": peaks[bound], "frac": own / peaks[bound],
+                                      "unit": "TFLOP/s" if kind == "fwd" else "GB/s"},
+                         "clocks": clk}
             del q, k, v
             torch.cuda.empty_cache()
         except Exception as e:  # noqa: BLE001 - a secondary line must not void the headline
@@ -437,11 +542,13 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": units["metric"], "value": value, "unit": units["unit"],
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * secs / max(1, args.steps), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        # time of ONE FULL step of the workload at the measured rate (each timed step is a bounded sample of it)
+        "ms_per_step": 1e3 * units["amount"] / value, "sample_ms_per_step": 1e3 * secs / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "fp32", "data": "synthetic",
-        "config": {"workload": f"{name}: {kind} B={B} Hq={Hq} Hkv={Hkv} N={S} d={D} causal={causal}",
-                   "note": "the reference ships no CPU kernel; its CPU path is the naive attention of "
-                           "examples/python/testFlashDecoder.py:84-92, restated in oracle/naive.py"},
+        "config": workload_config(name, int(os.environ.get("WORLD_SIZE", "1"))),
+        "note": "the reference ships no CPU kernel; its CPU path is the naive attention of "
+                "examples/python/testFlashDecoder.py:84-92, restated in oracle/naive.py; rank 0 runs it on all host cores",
         "cpu_baseline": {"value": value, "unit": units["unit"], "cores": r["cores"], "kind": "port", "sample": r["sample"] + " per step"},
         "e2e": {"value": value, "unit": units["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -459,6 +566,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-sustained", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SFA_ABI_VERSION 1
+#define SFA_ABI_VERSION 2
 
 typedef enum sfa_dtype { SFA_FP16 = 0, SFA_BF16 = 1 } sfa_dtype;
 
@@ -222,6 +222,29 @@ int sfa_rotary_table(void* cos_table, void* sin_table, int32_t max_seq_len, int3
                      int32_t dtype, void* stream);
 /* Fill n elements with a constant (the reference's test utility). */
 int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream);
+
+/* ---------------------------------------------------------------- host-buffer entry points ---
+ * The same operations on PINNED HOST tensors (cudaHostAlloc / cudaHostRegister): inputs are uploaded, the
+ * kernels run and the results are downloaded by one call, cut into pieces so that the upload of piece i+1, the
+ * kernel of piece i and the download of piece i-1 overlap on three streams (two are owned by the library, the
+ * kernels run on `stream`).  The results are complete once `stream` has been synchronised.  The reference's own
+ * host path is blocking cudaMemcpy calls and a device synchronise per call (src/flash_attn.cu:973-975,986).
+ * Every pointer of `t` is a host pointer; strides are in elements and describe the HOST tensors (a caller may pass a
+ * slice of the heads of a larger tensor: head stride must equal head_dim, batch / row strides are free); lse is
+ * (batch, heads_q, seqlen_q) resp. (batch, heads_q) fp32 contiguous or NULL.  pieces <= 0: library's choice
+ * (about 16 for prefill: (batch entry, block of query rows); 8 for decode: batch ranges).  Device staging is
+ * owned by the library (grow-only, per device; released by sfa_release_workspaces).  Not graph-capturable. */
+typedef struct sfa_fwd_host_args {
+    sfa_fwd_args t;
+    int32_t pieces;
+} sfa_fwd_host_args;
+int sfa_fwd_host(const sfa_fwd_host_args* args, void* stream);
+
+typedef struct sfa_decode_host_args {
+    sfa_decode_args t; /* workspace fields are ignored */
+    int32_t pieces;
+} sfa_decode_host_args;
+int sfa_decode_host(const sfa_decode_host_args* args, void* stream);
 
 /* ---------------------------------------------------------------- misc ---------------------- */
 /* Pitched copy between pinned host memory and the device on `stream` (cudaMemcpy2DAsync): `height` rows of

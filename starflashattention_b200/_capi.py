@@ -18,7 +18,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_paged",
+    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -58,6 +58,14 @@ class DecodeArgs(C.Structure):
         ("softmax_scale", C.c_float), ("num_splits", C.c_int32), ("dtype", C.c_int32),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
     ]
+
+
+class FwdHostArgs(C.Structure):
+    _fields_ = [("t", FwdArgs), ("pieces", C.c_int32)]
+
+
+class DecodeHostArgs(C.Structure):
+    _fields_ = [("t", DecodeArgs), ("pieces", C.c_int32)]
 
 
 class DecodePagedArgs(C.Structure):
@@ -118,6 +126,10 @@ def _load() -> C.CDLL:
     lib.sfa_decode.restype = C.c_int
     lib.sfa_decode_paged.argtypes = [C.POINTER(DecodePagedArgs), C.c_void_p]
     lib.sfa_decode_paged.restype = C.c_int
+    lib.sfa_fwd_host.argtypes = [C.POINTER(FwdHostArgs), C.c_void_p]
+    lib.sfa_fwd_host.restype = C.c_int
+    lib.sfa_decode_host.argtypes = [C.POINTER(DecodeHostArgs), C.c_void_p]
+    lib.sfa_decode_host.restype = C.c_int
     lib.sfa_copy_2d.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p]
     lib.sfa_copy_2d.restype = C.c_int
     lib.sfa_decode_num_splits.argtypes = [C.POINTER(DecodeArgs)]

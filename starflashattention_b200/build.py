@@ -24,7 +24,7 @@ LIB = os.path.join(PKG, "lib", "libStarFlashAttention.so")
 OBJ_PROBES = os.path.join(PKG, "lib", "obj_probes")
 LIB_PROBES = os.path.join(PKG, "lib", "libStarFlashAttention_probes.so")
 
-SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "fwd_sm100_v1.cu", "capi.cu"]
+SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "fwd_sm100_v1.cu", "host_pipeline.cu", "capi.cu"]
 HEADERS = [os.path.join(CSRC, "internal.h"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(CSRC, "rope.cuh"), os.path.join(CSRC, "merge.cuh"),
            os.path.join(ROOT, "include", "star_flash_attn.h"), os.path.join(ROOT, "include", "src", "flash_attn.h"),
            os.path.join(ROOT, "include", "src", "params.h"), os.path.join(ROOT, "include", "src", "traits.h")]

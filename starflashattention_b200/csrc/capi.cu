@@ -287,6 +287,16 @@ int sfa_decode_paged(const sfa_decode_paged_args* args, void* stream) {
     return sfa::decode_impl(args->base, 0, reinterpret_cast<cudaStream_t>(stream), nullptr, &pk);
 }
 
+int sfa_fwd_host(const sfa_fwd_host_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_fwd_host: null args");
+    return sfa::fwd_host_impl(args->t, args->pieces, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_decode_host(const sfa_decode_host_args* args, void* stream) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_host: null args");
+    return sfa::decode_host_impl(args->t, args->pieces, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int sfa_copy_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes, size_t height,
                 int32_t kind, void* stream) {
     if (!dst || !src) return sfa::fail(SFA_ERR_INVALID, "sfa_copy_2d: null pointer");

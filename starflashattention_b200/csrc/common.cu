@@ -157,6 +157,7 @@ const char* sfa_last_error(void) { return sfa::g_last_error.c_str(); }
 int sfa_abi_version(void) { return SFA_ABI_VERSION; }
 uint64_t sfa_launch_count(void) { return sfa::g_launches.load(); }
 void sfa_release_workspaces(void) {
+    sfa::release_host_pipelines();
     std::lock_guard<std::mutex> lk(sfa::g_mu);
     int cur = -1;
     cudaGetDevice(&cur);

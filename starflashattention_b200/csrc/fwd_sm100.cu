@@ -488,6 +488,38 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
 #ifdef SFA_PROBES
         const bool tr = trace_cta && lane == 0;
 #endif
+        // O(q) += P V of the tile whose Q.K was issued last; it is issued BEHIND the next tile's Q.K - also across an
+        // item boundary, so the scores of an item's first tile are on their way while the warpgroup still works on
+        // the previous item's last tile and epilogue.
+        struct Pending {
+            bool valid;
+            uint32_t gi;        // ring index of the tile's V
+            uint32_t t;         // running tile count (parity of p_ready)
+            bool accumulate;    // false for the first key tile of an item
+            int releases;       // arrivals on the ring slot this warp owes (its own plus absent query tiles')
+        } pend = {false, 0u, 0u, false, 0};
+        auto flush_pv = [&]() {   // in two halves of 64 keys
+            if (!pend.valid) return;
+            pend.valid = false;
+            const uint32_t vslot = pend.gi % NSTAGE;
+            ok = ok && wait_all(bar_kv_full(vslot), (pend.gi / NSTAGE) & 1, 4);
+            ok = ok && wait_all(bar_p_ready(q, 0), pend.t & 1, 5);
+            tc_fence_after();
+            SFA_TRACE(tr, pend.t, q, 3);
+            if (ok && elect_one()) issue_pv(vslot, 0, pend.accumulate);
+            __syncwarp();
+            ok = ok && wait_all(bar_p_ready(q, 1), pend.t & 1, 5);
+            tc_fence_after();
+            SFA_TRACE(tr, pend.t, q, 5);
+            if (ok && elect_one()) {
+                issue_pv(vslot, 1, true);
+                tc_commit(bar_pv_done(q));
+                if constexpr (!SOFTREL)
+                    for (int u = 0; u < pend.releases; ++u) tc_commit(bar_kv_empty(vslot));
+            }
+            __syncwarp();
+            SFA_TRACE(tr, pend.t, q, 6);
+        };
         for (int k = 0; ok; ++k) {
             const int item = next_item(k, ok);
             if (item >= p.total_items) break;
@@ -497,66 +529,59 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             if (n_q > 0) {
                 ok = wait_all(bar_q_full(q), q_uses & 1, 3);
                 ++q_uses;
+            } else {
+                flush_pv();   // an item this warp sits out: nothing to overlap with, and its ring slot must not be held
             }
-            for (int j = 0; j <= n_q && ok; ++j) {
+            for (int j = 0; j < n_q && ok; ++j) {
                 // ---- S(q, j) = Q_q K_j^T
-                if (j < n_q) {
-                    const uint32_t gi = ring + 2u * (uint32_t)j, kslot = gi % NSTAGE;
-                    const uint32_t t = tiles[q] + (uint32_t)j;      // running tile count of this query tile
-                    int buf = 0;
-                    ok = wait_all(bar_kv_full(kslot), (gi / NSTAGE) & 1, 2);
-                    SFA_TRACE(tr, t, q, 0);
-                    // the buffer's previous scores must have been loaded into registers by their warpgroup
-                    if constexpr (NQ == 2 && kSBufs == 1) {
-                        const int ord = qk_ordinal(it, q, j);
-                        if (ord >= 1) {
-                            const int prev = tile_of_ordinal(it, ord - 1);
-                            const int pq = prev >> 16;
-                            ok = ok && wait_all(bar_s_free(pq), (tiles[pq] + (uint32_t)(prev & 0xffff)) & 1, 9);
-                        } else if (has_last) {
-                            ok = ok && wait_all(bar_s_free(last_q), last_parity, 9);
-                        }
-                    } else if constexpr (NQ == 2) {
-                        buf = q;
-                        if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
-                    } else {
-                        buf = t & 1;
-                        if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
+                const uint32_t gi = ring + 2u * (uint32_t)j, kslot = gi % NSTAGE;
+                const uint32_t t = tiles[q] + (uint32_t)j;      // running tile count of this query tile
+                int buf = 0;
+                ok = wait_all(bar_kv_full(kslot), (gi / NSTAGE) & 1, 2);
+                SFA_TRACE(tr, t, q, 0);
+                // the buffer's previous scores must have been loaded into registers by their warpgroup
+                if constexpr (NQ == 2 && kSBufs == 1) {
+                    const int ord = qk_ordinal(it, q, j);
+                    if (ord >= 1) {
+                        const int prev = tile_of_ordinal(it, ord - 1);
+                        const int pq = prev >> 16;
+                        ok = ok && wait_all(bar_s_free(pq), (tiles[pq] + (uint32_t)(prev & 0xffff)) & 1, 9);
+                    } else if (has_last) {
+                        ok = ok && wait_all(bar_s_free(last_q), last_parity, 9);
                     }
-                    tc_fence_after();
-                    SFA_TRACE(tr, t, q, 1);
-                    if (ok && elect_one()) {
-                        issue_qk(kslot, buf);
-                        tc_commit(bar_s_full(q));
-                        if (j == n_q - 1) tc_commit(bar_q_empty(q));
-                        if constexpr (!SOFTREL)
-                            for (int u = users(it, j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
-                    }
-                    __syncwarp();
-                    SFA_TRACE(tr, t, q, 2);
+                } else if constexpr (NQ == 2) {
+                    buf = q;
+                    if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
+                } else {
+                    buf = t & 1;
+                    if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
                 }
-                // ---- O(q) += P(q, j-1) V_{j-1}, in two halves of 64 keys
-                if (ok && j > 0) {
-                    const uint32_t gi = ring + 2u * (uint32_t)(j - 1) + 1u, vslot = gi % NSTAGE;
-                    const uint32_t t = tiles[q] + (uint32_t)(j - 1);
-                    ok = wait_all(bar_kv_full(vslot), (gi / NSTAGE) & 1, 4);
-                    ok = ok && wait_all(bar_p_ready(q, 0), t & 1, 5);
-                    tc_fence_after();
-                    SFA_TRACE(tr, t, q, 3);
-                    if (ok && elect_one()) issue_pv(vslot, 0, j > 1);
-                    __syncwarp();
-                    ok = ok && wait_all(bar_p_ready(q, 1), t & 1, 5);
-                    tc_fence_after();
-                    SFA_TRACE(tr, t, q, 5);
-                    if (ok && elect_one()) {
-                        issue_pv(vslot, 1, true);
-                        tc_commit(bar_pv_done(q));
-                        if constexpr (!SOFTREL)
-                            for (int u = users(it, j - 1); u <= NQ; ++u) tc_commit(bar_kv_empty(vslot));
-                    }
-                    __syncwarp();
-                    SFA_TRACE(tr, t, q, 6);
+                tc_fence_after();
+                SFA_TRACE(tr, t, q, 1);
+                if (ok && elect_one()) {
+                    issue_qk(kslot, buf);
+                    tc_commit(bar_s_full(q));
+                    if (j == n_q - 1) tc_commit(bar_q_empty(q));
+                    if constexpr (!SOFTREL)
+                        for (int u = users(it, j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
                 }
+                __syncwarp();
+                SFA_TRACE(tr, t, q, 2);
+                // ---- P.V of the previous tile (the previous item's last one when j == 0)
+                flush_pv();
+                pend.valid = true;
+                pend.gi = gi + 1u;
+                pend.t = t;
+                pend.accumulate = j > 0;
+                pend.releases = NQ - users(it, j) + 1;
+            }
+            // A parity wait is only sound for a waiter that has seen the phase before: follow the phases of the ring
+            // loads this warp does not consume (key tiles only the other query tile needs), or a later wait on the
+            // same slot could take a stale phase for the one it wants.
+            for (int j = n_q; j < it.n_max && ok; ++j) {
+                const uint32_t gk = ring + 2u * (uint32_t)j, gv = gk + 1u;
+                ok = wait_all(bar_kv_full(gk % NSTAGE), (gk / NSTAGE) & 1, 14);
+                ok = ok && wait_all(bar_kv_full(gv % NSTAGE), (gv / NSTAGE) & 1, 14);
             }
             if constexpr (NQ == 2 && kSBufs == 1) {
                 const int total = it.n[0] + it.n[NQ - 1];
@@ -571,6 +596,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             for (int qq = 0; qq < NQ; ++qq) tiles[qq] += (uint32_t)it.n[qq];
             ring += 2u * (uint32_t)it.n_max;
         }
+        flush_pv();
     } else if (warp < kSoftmaxWarps) {
         // =============================================================== softmax warpgroups
         // Warpgroup q serves query tile q; thread i owns row i of the tile (TMEM lane i).
@@ -862,6 +888,14 @@ int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cuda
     p.m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     p.heads_total = batch * p.heads_q;
     p.group_heads = (2 * sm_count + p.m_blocks - 1) / p.m_blocks;
+    // ... but never more than 32 MB of K/V per group (one head's K/V: seqlen_k rows of D elements, twice): at
+    // N = 65536, d = 128 that is one head at a time, as many CTAs as there are SMs on the same 32 MB
+    const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;
+    const long long l2_heads = (32ll << 20) / kv_bytes_per_head;
+    if (p.group_heads > l2_heads) p.group_heads = (int)l2_heads;
+#ifdef SFA_PROBES
+    if (fwd_tuning().group > 0) p.group_heads = fwd_tuning().group;
+#endif
     if (p.group_heads < 1) p.group_heads = 1;
     // keep the query heads of one kv head in one group (GQA)
     p.group_heads = (p.group_heads + p.group - 1) / p.group * p.group;
@@ -915,6 +949,7 @@ const FwdTuning& fwd_tuning() {
         v.stagger = geti("SFA_FWD_STAGGER", -1);
         v.nq = geti("SFA_FWD_NQ", 0);
         v.v1 = geti("SFA_FWD_V1", 0);
+        v.group = geti("SFA_FWD_GROUP", 0);
         return v;
     }();
     return t;

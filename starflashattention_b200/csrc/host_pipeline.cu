@@ -1,0 +1,322 @@
+// Host-buffer entry points: pinned host tensors in, pinned host tensors out (sfa_fwd_host, sfa_decode_host).
+//
+// The reference's host layer moves its inputs with blocking cudaMemcpy calls and a cudaDeviceSynchronize per call
+// (src/flash_attn.cu:973-975,986) and its caller holds everything on the device; a caller whose tensors live in
+// host memory pays the PCIe time on top.  Here the independent units of a call are cut into pieces and the
+// host->device copy of piece i+1, the kernel of piece i and the device->host copy of piece i-1 run at the
+// same time on three streams (PCIe is full duplex), so a call costs about max(upload, download) + one piece.
+//
+// Prefill pieces are (batch entry, block of query rows), all heads: with every head in a piece the host rows are
+// contiguous, so each piece moves as plain 1-D copies (a caller that owns a slice of heads - a rank of the multi-GPU
+// driver - passes strided tensors and the same code issues pitched 2-D copies).  Under the causal mask a piece of rows
+// [r0, r1) needs keys [0, r1 + shift) only, so K/V travel incrementally, piece by piece, and the first kernel
+// starts after the first piece's upload; the kernel's bottom-right aligned mask makes "rows [r0, r1) against the
+// key prefix" exactly the rows of the full problem.
+#include "internal.h"
+
+#include <math.h>
+#include <mutex>
+#include <vector>
+
+namespace sfa {
+namespace {
+
+struct Pipeline {
+    std::mutex mu;                   // one call at a time enqueues on a device's pipeline
+    bool ready = false;
+    bool used = false;               // ev_last has been recorded: the next call orders itself behind it
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {}, ev_kv_done[2] = {};
+    // staging: [0..1] double buffers per kind; grown on demand, outgrown buffers are retired (work may be queued)
+    void* buf[8] = {};
+    size_t cap[8] = {};
+    std::vector<void*> retired;
+};
+enum { kQ0 = 0, kQ1, kO0, kO1, kKV0, kKV1, kL0, kL1 };   // Q, O, K+V, LSE (decode: q+seqlens, o+lse, caches)
+
+std::mutex g_pipes_mu;
+std::vector<Pipeline*> g_pipes;
+
+Pipeline* pipeline_for_current_device() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lk(g_pipes_mu);
+    if ((int)g_pipes.size() <= dev) g_pipes.resize(dev + 1, nullptr);
+    if (!g_pipes[dev]) g_pipes[dev] = new Pipeline();
+    return g_pipes[dev];
+}
+
+int pipeline_init(Pipeline& p) {
+    if (p.ready) return SFA_OK;
+    SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
+    SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
+    cudaEvent_t* evs[] = {&p.ev_start, &p.ev_last, &p.ev_in[0], &p.ev_in[1], &p.ev_comp[0], &p.ev_comp[1], &p.ev_out[0], &p.ev_out[1],
+                          &p.ev_kv_done[0], &p.ev_kv_done[1]};
+    for (cudaEvent_t* e : evs) SFA_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    p.ready = true;
+    return SFA_OK;
+}
+
+int ensure(Pipeline& p, int which, size_t bytes) {
+    if (p.cap[which] >= bytes) return SFA_OK;
+    if (p.buf[which]) p.retired.push_back(p.buf[which]);
+    p.buf[which] = nullptr;
+    p.cap[which] = 0;
+    const size_t want = bytes + bytes / 8;
+    SFA_CUDA_CHECK(cudaMalloc(&p.buf[which], want));
+    p.cap[which] = want;
+    return SFA_OK;
+}
+
+// rows x width_bytes between host and device; one plain copy when both sides are dense
+int copy_rows(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width, size_t rows,
+              cudaMemcpyKind kind, cudaStream_t s) {
+    if (rows == 0 || width == 0) return SFA_OK;
+    if (dst_pitch == width && src_pitch == width) SFA_CUDA_CHECK(cudaMemcpyAsync(dst, src, width * rows, kind, s));
+    else SFA_CUDA_CHECK(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width, rows, kind, s));
+    return SFA_OK;
+}
+
+int check_pinned(const void* p, const char* what) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess || at.type != cudaMemoryTypeHost) {
+        cudaGetLastError();
+        return fail(SFA_ERR_INVALID, std::string(what) + " must point to pinned host memory (cudaHostAlloc / cudaHostRegister)");
+    }
+    return SFA_OK;
+}
+
+}  // namespace
+
+int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
+    if (!a.q || !a.k || !a.v || !a.o) return fail(SFA_ERR_INVALID, "fwd_host: null tensor pointer");
+    if (a.batch < 0 || a.seqlen_q < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0 || a.heads_q % a.heads_kv)
+        return fail(SFA_ERR_INVALID, "fwd_host: bad dimension");
+    if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "fwd_host: head_dim must be 64 or 128");
+    if (a.dtype != SFA_FP16 && a.dtype != SFA_BF16) return fail(SFA_ERR_INVALID, "fwd_host: dtype must be fp16 or bf16");
+    const int B = a.batch, Sq = a.seqlen_q, Sk = a.seqlen_k, Hq = a.heads_q, Hkv = a.heads_kv, D = a.head_dim;
+    // heads of a token must be dense (head stride == head_dim): a token's heads are one DMA row
+    if (a.q_head_stride != D || a.k_head_stride != D || a.v_head_stride != D || a.o_head_stride != D)
+        return fail(SFA_ERR_INVALID, "fwd_host: the heads of a token must be contiguous (head stride == head_dim)");
+    if (B == 0 || Sq == 0) return SFA_OK;
+    int rc;
+    if ((rc = check_pinned(a.q, "fwd_host: q")) || (rc = check_pinned(a.k, "fwd_host: k")) ||
+        (rc = check_pinned(a.v, "fwd_host: v")) || (rc = check_pinned(a.o, "fwd_host: o")))
+        return rc;
+    if (a.lse && (rc = check_pinned(a.lse, "fwd_host: lse"))) return rc;
+    if (!current_device()) return SFA_ERR_NO_DEVICE;
+    Pipeline* pp = pipeline_for_current_device();
+    if (!pp) return fail(SFA_ERR_CUDA, "fwd_host: no current device");
+    std::lock_guard<std::mutex> lk(pp->mu);
+    Pipeline& P = *pp;
+    if ((rc = pipeline_init(P))) return rc;
+
+    // ---- plan: pieces = (batch entry, block of query rows)
+    if (want_pieces <= 0) want_pieces = 16;
+    int n_r = (want_pieces + B - 1) / B;
+    int rows_per = (Sq + n_r - 1) / n_r;
+    rows_per = (rows_per + 255) / 256 * 256;              // whole 256-row blocks of the kernel
+    n_r = (Sq + rows_per - 1) / rows_per;
+    const int shift = Sk - Sq;
+    const size_t es = 2;
+    const size_t q_row = (size_t)Hq * D * es, kv_row = (size_t)Hkv * D * es;
+    if ((rc = ensure(P, kQ0, rows_per * q_row)) || (rc = ensure(P, kQ1, rows_per * q_row)) ||
+        (rc = ensure(P, kO0, rows_per * q_row)) || (rc = ensure(P, kO1, rows_per * q_row)) ||
+        (rc = ensure(P, kKV0, 2 * (size_t)Sk * kv_row + 256)) || (rc = ensure(P, kL0, (size_t)Hq * rows_per * 4)) ||
+        (rc = ensure(P, kL1, (size_t)Hq * rows_per * 4)))
+        return rc;
+    if (B > 1 && (rc = ensure(P, kKV1, 2 * (size_t)Sk * kv_row + 256))) return rc;
+
+    // the previous call (maybe on another stream) may still be using the staging buffers
+    if (P.used) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_last, 0));
+    SFA_CUDA_CHECK(cudaEventRecord(P.ev_start, cur));
+    SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
+    SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_start, 0));
+    const uint8_t* hq = reinterpret_cast<const uint8_t*>(a.q);
+    const uint8_t* hk = reinterpret_cast<const uint8_t*>(a.k);
+    const uint8_t* hv = reinterpret_cast<const uint8_t*>(a.v);
+    uint8_t* ho = reinterpret_cast<uint8_t*>(a.o);
+    int piece = 0;
+    bool comp_used[2] = {false, false}, out_used[2] = {false, false}, kv_used[2] = {false, false};
+    for (int b = 0; b < B; ++b) {
+        const int kvb = b & 1;
+        uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + kvb]);
+        uint8_t* dV = dK + ((size_t)Sk * kv_row + 255) / 256 * 256;
+        // the K/V buffer of entry b was last read by the kernels of entry b - 2
+        if (kv_used[kvb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb], 0));
+        int keys_up = 0;   // keys of this entry already on the device
+        for (int r = 0; r < n_r; ++r, ++piece) {
+            const int r0 = r * rows_per, r1 = Sq < r0 + rows_per ? Sq : r0 + rows_per, rows = r1 - r0;
+            int keys = a.causal ? r1 + shift : Sk;       // keys [0, keys) are visible to rows < r1
+            keys = keys < 0 ? 0 : (keys > Sk ? Sk : keys);
+            const int pb = piece & 1;
+            uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
+            uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
+            float* dL = reinterpret_cast<float*>(P.buf[kL0 + pb]);
+            // ---- upload: the piece's Q rows and the K/V rows it is the first to need
+            if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
+            if ((rc = copy_rows(dQ, q_row, hq + es * ((size_t)b * a.q_batch_stride + (size_t)r0 * a.q_row_stride),
+                                es * a.q_row_stride, q_row, rows, cudaMemcpyHostToDevice, P.s_in)))
+                return rc;
+            if (keys > keys_up) {
+                const size_t n = (size_t)(keys - keys_up);
+                if ((rc = copy_rows(dK + keys_up * kv_row, kv_row, hk + es * ((size_t)b * a.k_batch_stride + (size_t)keys_up * a.k_row_stride),
+                                    es * a.k_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)) ||
+                    (rc = copy_rows(dV + keys_up * kv_row, kv_row, hv + es * ((size_t)b * a.v_batch_stride + (size_t)keys_up * a.v_row_stride),
+                                    es * a.v_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)))
+                    return rc;
+                keys_up = keys;
+            }
+            SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
+            // ---- kernel
+            SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
+            if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
+            sfa_fwd_args d = {};
+            d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
+            d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = Hq; d.heads_kv = Hkv; d.head_dim = D;
+            d.q_batch_stride = (int64_t)rows * Hq * D; d.q_row_stride = (int64_t)Hq * D; d.q_head_stride = D;
+            d.k_batch_stride = (int64_t)Sk * Hkv * D; d.k_row_stride = (int64_t)Hkv * D; d.k_head_stride = D;
+            d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
+            d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
+            d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
+            if ((rc = launch_fwd(d, cur))) return rc;
+            SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
+            comp_used[pb] = true;
+            // ---- download
+            SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
+            if ((rc = copy_rows(ho + es * ((size_t)b * a.o_batch_stride + (size_t)r0 * a.o_row_stride), es * a.o_row_stride,
+                                dO, q_row, q_row, rows, cudaMemcpyDeviceToHost, P.s_out)))
+                return rc;
+            if (a.lse)   // host (batch, heads, Sq) fp32: one row of `rows` floats per head
+                if ((rc = copy_rows(a.lse + ((size_t)b * Hq) * Sq + r0, (size_t)Sq * 4, dL, (size_t)rows * 4, (size_t)rows * 4,
+                                    Hq, cudaMemcpyDeviceToHost, P.s_out)))
+                    return rc;
+            SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
+            out_used[pb] = true;
+        }
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb], cur));
+        kv_used[kvb] = true;
+    }
+    for (int i = 0; i < 2; ++i)
+        if (out_used[i]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[i], 0));
+    SFA_CUDA_CHECK(cudaEventRecord(P.ev_last, cur));
+    P.used = true;
+    return SFA_OK;
+}
+
+// Split-KV decode on pinned host tensors: the batch is cut into pieces whose cache upload overlaps the previous
+// piece's kernel and download.
+int decode_host_impl(const sfa_decode_args& a, int want_pieces, cudaStream_t cur) {
+    if (!a.q || !a.k_cache || !a.v_cache || !a.o) return fail(SFA_ERR_INVALID, "decode_host: null tensor pointer");
+    if (a.batch < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0 || a.heads_q % a.heads_kv)
+        return fail(SFA_ERR_INVALID, "decode_host: bad dimension");
+    if (a.dtype != SFA_FP16 && a.dtype != SFA_BF16) return fail(SFA_ERR_INVALID, "decode_host: dtype must be fp16 or bf16");
+    const int B = a.batch, M = a.seqlen_k, Hq = a.heads_q, Hkv = a.heads_kv, D = a.head_dim;
+    if (a.q_head_stride != D || a.k_head_stride != D || a.v_head_stride != D || a.o_head_stride != D)
+        return fail(SFA_ERR_INVALID, "decode_host: the heads of a token must be contiguous (head stride == head_dim)");
+    if (B == 0) return SFA_OK;
+    int rc;
+    if ((rc = check_pinned(a.q, "decode_host: q")) || (rc = check_pinned(a.k_cache, "decode_host: k_cache")) ||
+        (rc = check_pinned(a.v_cache, "decode_host: v_cache")) || (rc = check_pinned(a.o, "decode_host: o")))
+        return rc;
+    if (a.seqlens && (rc = check_pinned(a.seqlens, "decode_host: seqlens"))) return rc;
+    if (a.lse && (rc = check_pinned(a.lse, "decode_host: lse"))) return rc;
+    if (!current_device()) return SFA_ERR_NO_DEVICE;
+    Pipeline* pp = pipeline_for_current_device();
+    if (!pp) return fail(SFA_ERR_CUDA, "decode_host: no current device");
+    std::lock_guard<std::mutex> lk(pp->mu);
+    Pipeline& P = *pp;
+    if ((rc = pipeline_init(P))) return rc;
+
+    if (want_pieces <= 0) want_pieces = 8;
+    const int n = want_pieces < B ? want_pieces : B;
+    const int step = (B + n - 1) / n;
+    const size_t es = 2, q_row = (size_t)Hq * D * es, kv_row = (size_t)Hkv * D * es;
+    const size_t q_bytes = ((size_t)step * q_row + 255) / 256 * 256, cache_bytes = ((size_t)step * M * kv_row + 255) / 256 * 256;
+    for (int i = 0; i < 2; ++i) {
+        if ((rc = ensure(P, kQ0 + i, q_bytes + (size_t)step * 4 + 256)) ||                 // q, seqlens
+            (rc = ensure(P, kO0 + i, q_bytes + (size_t)step * Hq * 4 + 256)) ||               // o, lse
+            (rc = ensure(P, kKV0 + i, 2 * cache_bytes)))
+            return rc;
+    }
+    // the previous call (maybe on another stream) may still be using the staging buffers
+    if (P.used) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_last, 0));
+    SFA_CUDA_CHECK(cudaEventRecord(P.ev_start, cur));
+    SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
+    SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_start, 0));
+    bool comp_used[2] = {false, false}, out_used[2] = {false, false};
+    int piece = 0;
+    for (int lo = 0; lo < B; lo += step, ++piece) {
+        const int w = (B - lo < step) ? B - lo : step, pb = piece & 1;
+        uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
+        int32_t* dS = reinterpret_cast<int32_t*>(dQ + q_bytes);
+        uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
+        float* dL = reinterpret_cast<float*>(dO + q_bytes);
+        uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + pb]);
+        uint8_t* dV = dK + cache_bytes;
+        if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
+        if ((rc = copy_rows(dQ, q_row, reinterpret_cast<const uint8_t*>(a.q) + es * (size_t)lo * a.q_batch_stride,
+                            es * a.q_batch_stride, q_row, w, cudaMemcpyHostToDevice, P.s_in)))
+            return rc;
+        for (int b = 0; b < w; ++b) {   // a sequence's cache: M rows of all kv heads
+            if ((rc = copy_rows(dK + (size_t)b * M * kv_row, kv_row,
+                                reinterpret_cast<const uint8_t*>(a.k_cache) + es * (size_t)(lo + b) * a.k_batch_stride,
+                                es * a.k_row_stride, kv_row, M, cudaMemcpyHostToDevice, P.s_in)) ||
+                (rc = copy_rows(dV + (size_t)b * M * kv_row, kv_row,
+                                reinterpret_cast<const uint8_t*>(a.v_cache) + es * (size_t)(lo + b) * a.v_batch_stride,
+                                es * a.v_row_stride, kv_row, M, cudaMemcpyHostToDevice, P.s_in)))
+                return rc;
+        }
+        if (a.seqlens) SFA_CUDA_CHECK(cudaMemcpyAsync(dS, a.seqlens + lo, (size_t)w * 4, cudaMemcpyHostToDevice, P.s_in));
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
+        SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
+        if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
+        sfa_decode_args d = {};
+        d.q = dQ; d.k_cache = dK; d.v_cache = dV; d.seqlens = a.seqlens ? dS : nullptr; d.o = dO; d.lse = a.lse ? dL : nullptr;
+        d.batch = w; d.seqlen_k = M; d.heads_q = Hq; d.heads_kv = Hkv; d.head_dim = D;
+        d.q_batch_stride = (int64_t)Hq * D; d.q_head_stride = D;
+        d.k_batch_stride = (int64_t)M * Hkv * D; d.k_row_stride = (int64_t)Hkv * D; d.k_head_stride = D;
+        d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
+        d.o_batch_stride = (int64_t)Hq * D; d.o_head_stride = D;
+        d.softmax_scale = a.softmax_scale; d.num_splits = a.num_splits; d.dtype = a.dtype;
+        d.workspace = nullptr; d.workspace_bytes = 0;   // split partials: the stream's own library scratch
+        if ((rc = sfa_decode(&d, cur))) return rc;
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
+        comp_used[pb] = true;
+        SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
+        if ((rc = copy_rows(reinterpret_cast<uint8_t*>(a.o) + es * (size_t)lo * a.o_batch_stride, es * a.o_batch_stride, dO, q_row,
+                            q_row, w, cudaMemcpyDeviceToHost, P.s_out)))
+            return rc;
+        if (a.lse) SFA_CUDA_CHECK(cudaMemcpyAsync(a.lse + (size_t)lo * Hq, dL, (size_t)w * Hq * 4, cudaMemcpyDeviceToHost, P.s_out));
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
+        out_used[pb] = true;
+    }
+    for (int i = 0; i < 2; ++i)
+        if (out_used[i]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[i], 0));
+    SFA_CUDA_CHECK(cudaEventRecord(P.ev_last, cur));
+    P.used = true;
+    return SFA_OK;
+}
+
+void release_host_pipelines() {
+    std::lock_guard<std::mutex> lk(g_pipes_mu);
+    int cur = -1;
+    cudaGetDevice(&cur);
+    for (size_t i = 0; i < g_pipes.size(); ++i) {
+        Pipeline* p = g_pipes[i];
+        if (!p) continue;
+        std::lock_guard<std::mutex> lk2(p->mu);
+        cudaSetDevice((int)i);
+        cudaDeviceSynchronize();
+        for (int b = 0; b < 8; ++b) {
+            if (p->buf[b]) cudaFree(p->buf[b]);
+            p->buf[b] = nullptr;
+            p->cap[b] = 0;
+        }
+        for (void* r : p->retired) cudaFree(r);
+        p->retired.clear();
+    }
+    if (cur >= 0) cudaSetDevice(cur);
+}
+
+}  // namespace sfa

@@ -103,7 +103,7 @@ int fwd_error_flag_read_v1(int* value);
 int fwd_error_flag_clear_v1();
 // Tuning overrides of the prefill launcher, read from the environment once per process.
 struct FwdTuning {
-    int poly = -1, softrel = -1, stagger = -1, nq = 0, v1 = 0;
+    int poly = -1, softrel = -1, stagger = -1, nq = 0, v1 = 0, group = 0;
 };
 const FwdTuning& fwd_tuning();
 // Two zeroed ints (next-item counter, CTAs done) for one launch of the persistent prefill kernel; the kernel
@@ -115,5 +115,10 @@ int fwd_sched_reset();
 int fwd_error_flag_read(int* value);
 int fwd_error_flag_clear();
 int fwd_probe_read(unsigned long long* out, int n);
+
+// ------------------------------------------------------------------ host-buffer pipeline (host_pipeline.cu)
+int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t stream);
+int decode_host_impl(const sfa_decode_args& a, int want_pieces, cudaStream_t stream);
+void release_host_pipelines();
 
 }  // namespace sfa

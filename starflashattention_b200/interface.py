@@ -368,28 +368,9 @@ def launch_count() -> int:
 
 
 # ------------------------------------------------------------------------------------------------
-# Host-buffer entry points: pinned host tensors in, pinned host tensors out.  The (batch x head) units are
-# independent, so the work is cut into chunks and the host->device copy of chunk i+1, the kernel of chunk i and
-# the device->host copy of chunk i-1 run concurrently on three streams (PCIe is full duplex).
-class _HostPipeline:
-    """Double-buffered device staging for one (shape, dtype, device) signature; cached, grow-never."""
-    _cache = {}
-
-    def __init__(self, dev, shapes_dtypes):
-        self.bufs = [[torch.empty(s, dtype=d, device=dev) for (s, d) in shapes_dtypes] for _ in range(2)]
-        self.s_in = torch.cuda.Stream(device=dev)
-        self.s_out = torch.cuda.Stream(device=dev)
-
-    @classmethod
-    def get(cls, dev, key, shapes_dtypes):
-        k = (dev, key)
-        if k not in cls._cache:
-            if len(cls._cache) >= 8:
-                cls._cache.clear()
-            cls._cache[k] = cls(dev, shapes_dtypes)
-        return cls._cache[k]
-
-
+# Host-buffer entry points: pinned host tensors in, pinned host tensors out.  The pipeline itself (piece plan, three
+# streams, device staging) lives in the library (sfa_fwd_host / sfa_decode_host, csrc/host_pipeline.cu); these are
+# thin callers, as the reference's Python layer is over its C++ host layer (src/flash_api.cpp:42-68).
 def _pinned(t: torch.Tensor, what: str):
     if t.is_cuda:
         raise ValueError(f"{what} must be a host tensor (use fwd()/decode() for device tensors)")
@@ -397,107 +378,42 @@ def _pinned(t: torch.Tensor, what: str):
         raise ValueError(f"{what} must live in pinned host memory (tensor.pin_memory())")
 
 
-def _copy_heads(dst: torch.Tensor, src: torch.Tensor, to_device: bool, stream) -> None:
-    """Copy a slice of heads of a (batch, seqlen, heads, head_dim) tensor between pinned host memory and the device
-    as ONE pitched DMA (sfa_copy_2d).  `tensor.copy_` of such a view first gathers it on the host into pageable
-    memory and stalls the pipeline (measured: 4 GB/s against ~50 GB/s).  Both tensors must have uniform row
-    pitches, i.e. (batch, seqlen) must flatten to rows `stride(1)` apart."""
-    def rows(t):
-        if t.stride(3) != 1 or t.stride(2) != t.shape[3] or (t.shape[0] > 1 and t.stride(0) != t.shape[1] * t.stride(1)):
-            raise ValueError("not a pitched (batch, seqlen, heads, head_dim) view")
-        return t.shape[0] * t.shape[1], t.stride(1) * t.element_size(), t.shape[2] * t.shape[3] * t.element_size()
-    n_d, pitch_d, width_d = rows(dst)
-    n_s, pitch_s, width_s = rows(src)
-    if (n_d, width_d) != (n_s, width_s):
-        raise ValueError("shape mismatch in a pitched copy")
-    check(lib.sfa_copy_2d(dst.data_ptr(), pitch_d, src.data_ptr(), pitch_s, width_d, n_d, 1 if to_device else 2,
-                          stream.cuda_stream))
-
-
 def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = False,
              softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
              lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
     """Prefill forward on pinned HOST tensors: q (B,Sq,Hq,D), k/v (B,Sk,Hkv,D) -> (out, lse) in pinned host memory.
+    q/k/v/out may be slices of the heads of larger tensors (a rank's share); lse is dense (B,Hq,Sq).
+    ``chunks``: number of pieces the call is cut into (default: about 16).
     Asynchronous: the results are complete once the current stream of ``device`` has been synchronised."""
     for t, n in ((q, "q"), (k, "k"), (v, "v")):
         _pinned(t, n)
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     B, Sq, Hq, D = q.shape
-    _, Sk, Hkv, _ = k.shape
     if out is None:
         out = torch.empty(q.shape, dtype=q.dtype, pin_memory=True)
     if lse is None:
         lse = torch.empty((B, Hq, Sq), dtype=torch.float32, pin_memory=True)
-    g = Hq // Hkv
-    # Chunks are (batch range) x (kv-head range).  A partial head range is moved with pitched DMAs (_copy_heads), kept
-    # at least 1 KB wide per row; 16 chunks by default (8 for one sequence) keep the exposed first upload and last
-    # download small against the PCIe time of the whole call.
-    want = chunks if chunks else (16 if B > 1 else 8)
-    n_b = max(1, min(B, want))
-    n_h = max(1, min(Hkv, want // n_b))
-    if not chunks:                      # the 1 KB floor applies to the default only: an explicit count is obeyed
-        n_h = max(1, min(n_h, (Hkv * D * q.element_size()) // 1024))
-    cb, ch = (B + n_b - 1) // n_b, (Hkv + n_h - 1) // n_h
-    pipe = _HostPipeline.get(dev, ("fwd", q.dtype, cb, Sq, Sk, ch, g, D),
-                             [((cb * Sq * ch * g * D,), q.dtype), ((cb * Sk * ch * D,), k.dtype),
-                              ((cb * Sk * ch * D,), v.dtype), ((cb * Sq * ch * g * D,), q.dtype),
-                              ((cb * ch * g * Sq,), torch.float32)])
+    _pinned(out, "out"); _pinned(lse, "lse")
+    if not lse.is_contiguous() or tuple(lse.shape) != (B, Hq, Sq) or lse.dtype != torch.float32:
+        raise ValueError("lse must be a contiguous float32 (batch, heads_q, seqlen_q) tensor")
+    if q.dtype != k.dtype or q.dtype != v.dtype or out.dtype != q.dtype or out.shape != q.shape:
+        raise TypeError("q, k, v, out must share one dtype and out must look like q")
+    for t in (q, k, v, out):
+        if t.stride(3) != 1:
+            raise ValueError("the head_dim axis must be contiguous")
+    h = _capi.FwdHostArgs()
+    a = h.t
+    a.q, a.k, a.v, a.o, a.lse = q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr()
+    a.batch, a.seqlen_q, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = B, Sq, k.shape[1], Hq, k.shape[2], D
+    a.q_batch_stride, a.q_row_stride, a.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
+    a.k_batch_stride, a.k_row_stride, a.k_head_stride = k.stride(0), k.stride(1), k.stride(2)
+    a.v_batch_stride, a.v_row_stride, a.v_head_stride = v.stride(0), v.stride(1), v.stride(2)
+    a.o_batch_stride, a.o_row_stride, a.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+    a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
+    a.causal, a.dtype = (1 if causal else 0), _dtype_code(q)
+    h.pieces = int(chunks) if chunks else 0
     with torch.cuda.device(dev):
-        cur = torch.cuda.current_stream()
-        start = torch.cuda.Event(); start.record(cur)
-        pipe.s_in.wait_event(start); pipe.s_out.wait_event(start)
-        ev_comp = [None, None]      # kernel done with staging buffer i (inputs reusable)
-        ev_out = [None, None]       # D2H done with staging buffer i (outputs reusable)
-        pieces = [(b0, min(B, b0 + cb), h0, min(Hkv, h0 + ch)) for b0 in range(0, B, cb) for h0 in range(0, Hkv, ch)]
-        for i, (b0, b1, h0, h1) in enumerate(pieces):
-            fq, fk, fv, fo, fl = pipe.bufs[i & 1]
-            whole = h0 == 0 and h1 == Hkv          # every head: the rows are contiguous, plain copies
-            src = (q[b0:b1, :, h0 * g:h1 * g], k[b0:b1, :, h0:h1], v[b0:b1, :, h0:h1])
-            dst_o, dst_l = out[b0:b1, :, h0 * g:h1 * g], lse[b0:b1, h0 * g:h1 * g]
-            bs, hq_c, hk_c = b1 - b0, (h1 - h0) * g, h1 - h0
-            dq = fq[: bs * Sq * hq_c * D].view(bs, Sq, hq_c, D)
-            dk = fk[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
-            dv = fv[: bs * Sk * hk_c * D].view(bs, Sk, hk_c, D)
-            do = fo[: bs * Sq * hq_c * D].view(bs, Sq, hq_c, D)
-            dl = fl[: bs * hq_c * Sq].view(bs, hq_c, Sq)
-            with torch.cuda.stream(pipe.s_in):
-                if ev_comp[i & 1] is not None:
-                    pipe.s_in.wait_event(ev_comp[i & 1])
-                if whole:
-                    dq.copy_(src[0], non_blocking=True); dk.copy_(src[1], non_blocking=True); dv.copy_(src[2], non_blocking=True)
-                else:      # a slice of heads: one pitched DMA per tensor
-                    for d_t, s_t in zip((dq, dk, dv), src):
-                        _copy_heads(d_t, s_t, True, pipe.s_in)
-                ev_in = torch.cuda.Event(); ev_in.record(pipe.s_in)
-            cur.wait_event(ev_in)
-            if ev_out[i & 1] is not None:
-                cur.wait_event(ev_out[i & 1])
-            a = FwdArgs()
-            a.q, a.k, a.v, a.o, a.lse = dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), do.data_ptr(), dl.data_ptr()
-            a.batch, a.seqlen_q, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = dq.shape[0], Sq, Sk, dq.shape[2], dk.shape[2], D
-            a.q_batch_stride, a.q_row_stride, a.q_head_stride = dq.stride(0), dq.stride(1), dq.stride(2)
-            a.k_batch_stride, a.k_row_stride, a.k_head_stride = dk.stride(0), dk.stride(1), dk.stride(2)
-            a.v_batch_stride, a.v_row_stride, a.v_head_stride = dv.stride(0), dv.stride(1), dv.stride(2)
-            a.o_batch_stride, a.o_row_stride, a.o_head_stride = do.stride(0), do.stride(1), do.stride(2)
-            a.softmax_scale = float(softmax_scale) if softmax_scale is not None else 0.0
-            a.causal, a.dtype = (1 if causal else 0), _dtype_code(q)
-            check(lib.sfa_fwd(a, cur.cuda_stream))
-            ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
-            with torch.cuda.stream(pipe.s_out):
-                pipe.s_out.wait_event(ev_comp[i & 1])
-                if whole:
-                    dst_o.copy_(do, non_blocking=True)
-                else:
-                    _copy_heads(dst_o, do, False, pipe.s_out)
-                if bs == 1 or whole:
-                    dst_l.copy_(dl, non_blocking=True)      # contiguous on the host
-                else:
-                    for bb in range(bs):                    # (heads, Sq) blocks of different sequences
-                        dst_l[bb].copy_(dl[bb], non_blocking=True)
-                ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
-        for e in ev_out:
-            if e is not None:
-                cur.wait_event(e)
+        check(lib.sfa_fwd_host(h, _stream()))
     return out, lse
 
 
@@ -505,56 +421,26 @@ def decode_host(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, s
                 softmax_scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
                 lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
     """Split-KV decode on pinned HOST tensors: q (B,Hq,D), caches (B,M,Hkv,D), seqlens int32 (B) or None ->
-    (out, lse) in pinned host memory.  The batch is cut into chunks whose cache upload overlaps the previous
-    chunk's kernel and download.  Asynchronous on the current stream of ``device``."""
+    (out, lse) in pinned host memory.  The batch is cut into pieces whose cache upload overlaps the previous
+    piece's kernel and download.  Asynchronous on the current stream of ``device``."""
     for t, n in ((q, "q"), (k_cache, "k_cache"), (v_cache, "v_cache")):
         _pinned(t, n)
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     B, Hq, D = q.shape
-    _, M, Hkv, _ = k_cache.shape
     if seqlens is not None:
         _pinned(seqlens, "seqlens")
-        if seqlens.dtype != torch.int32 or seqlens.numel() != B:
-            raise ValueError("seqlens must be an int32 tensor of shape (batch,)")
+        if seqlens.dtype != torch.int32 or seqlens.numel() != B or not seqlens.is_contiguous():
+            raise ValueError("seqlens must be a contiguous int32 tensor of shape (batch,)")
     if out is None:
         out = torch.empty(q.shape, dtype=q.dtype, pin_memory=True)
     if lse is None:
         lse = torch.empty((B, Hq), dtype=torch.float32, pin_memory=True)
-    n = min(chunks, B) if chunks else min(B, 8)
-    step = (B + n - 1) // n
-    pipe = _HostPipeline.get(dev, ("decode", q.dtype, step, M, Hq, Hkv, D),
-                             [((step, Hq, D), q.dtype), ((step, M, Hkv, D), q.dtype), ((step, M, Hkv, D), q.dtype),
-                              ((step,), torch.int32), ((step, Hq, D), q.dtype), ((step, Hq), torch.float32)])
+    _pinned(out, "out"); _pinned(lse, "lse")
+    if not lse.is_contiguous() or lse.dtype != torch.float32:
+        raise ValueError("lse must be a contiguous float32 (batch, heads_q) tensor")
+    h = _capi.DecodeHostArgs()
+    h.t = _decode_args(q, k_cache, v_cache, seqlens, out, lse, softmax_scale, 0)
+    h.pieces = int(chunks) if chunks else 0
     with torch.cuda.device(dev):
-        cur = torch.cuda.current_stream()
-        start = torch.cuda.Event(); start.record(cur)
-        pipe.s_in.wait_event(start); pipe.s_out.wait_event(start)
-        ev_comp, ev_out = [None, None], [None, None]
-        for i, lo in enumerate(range(0, B, step)):
-            hi = min(B, lo + step)
-            w = hi - lo
-            dq, dk, dv, dsl, do, dl = (t[:w] for t in pipe.bufs[i & 1])
-            with torch.cuda.stream(pipe.s_in):
-                if ev_comp[i & 1] is not None:
-                    pipe.s_in.wait_event(ev_comp[i & 1])
-                dq.copy_(q[lo:hi], non_blocking=True)
-                dk.copy_(k_cache[lo:hi], non_blocking=True)
-                dv.copy_(v_cache[lo:hi], non_blocking=True)
-                if seqlens is not None:
-                    dsl.copy_(seqlens[lo:hi], non_blocking=True)
-                ev_in = torch.cuda.Event(); ev_in.record(pipe.s_in)
-            cur.wait_event(ev_in)
-            if ev_out[i & 1] is not None:
-                cur.wait_event(ev_out[i & 1])
-            a = _decode_args(dq, dk, dv, dsl if seqlens is not None else None, do, dl, softmax_scale, 0)
-            check(lib.sfa_decode(a, cur.cuda_stream))
-            ev_comp[i & 1] = torch.cuda.Event(); ev_comp[i & 1].record(cur)
-            with torch.cuda.stream(pipe.s_out):
-                pipe.s_out.wait_event(ev_comp[i & 1])
-                out[lo:hi].copy_(do, non_blocking=True)
-                lse[lo:hi].copy_(dl, non_blocking=True)
-                ev_out[i & 1] = torch.cuda.Event(); ev_out[i & 1].record(pipe.s_out)
-        for e in ev_out:
-            if e is not None:
-                cur.wait_event(e)
+        check(lib.sfa_decode_host(h, _stream()))
     return out, lse

@@ -37,7 +37,7 @@ def test_reference_mangled_symbols_present(built_library):
 
 def test_abi_version_and_struct_sizes(built_library):
     from starflashattention_b200 import _capi
-    assert _capi.lib.sfa_abi_version() == 1
+    assert _capi.lib.sfa_abi_version() == 2
     # offsets implied by include/star_flash_attn.h (LP64): 5 pointers, 6 int32, 12 int64, float + 2 int32 (+pad)
     assert ctypes.sizeof(_capi.FwdArgs) == 5 * 8 + 6 * 4 + 12 * 8 + 4 + 2 * 4 + 4
     assert ctypes.sizeof(_capi.DecodeArgs) == 6 * 8 + 5 * 4 + 4 + 10 * 8 + 3 * 4 + 4 + 8 + 8

@@ -29,7 +29,7 @@ def test_mangled_entry_points_match_c_abi(built_library):
     assert r.returncode == 0, r.stdout + r.stderr
     assert "all mangled entry points match the C ABI" in r.stdout
     for what in ("run_flash_decoder<half> O", "run_flash_fwd<half> O", "run_flash_fwd<bf16> O",
-                 "run_flash_decode<half> O", "run_flash_decode<bf16> O", "K cache after the append"):
+                 "run_flash_decode<half> O", "run_flash_decode<bf16> O", "run_flash_decoder<half> K cache after the append"):
         assert f"[equal] {what}" in r.stdout, r.stdout
 
 
