@@ -265,6 +265,12 @@ int sfa_fwd_watchdog(int clear);
 /* Tuning aid: cycle counters written by the instrumented prefill build (SFA_FWD_DBG=5, tools/fwd_probe.py);
  * copies min(n, 32) 64-bit counters after synchronising the device. */
 int sfa_fwd_probe_read(uint64_t* out, int32_t n);
+/* Test / tuning aid: sets one of the library's A-B switches for the rest of the process (they start from the
+ * SFA_* environment variables, read once): "decode_cluster" (1: 2..8 splits merge in a thread-block cluster; 0:
+ * partials + combine launch), "decode_pdl" (0..2), "decode_waves", "decode_ctas", "decoder_fused" (1: RoPE +
+ * append inside the decode kernel; 0: stand-alone kernel first), "decode_swap" (0 in the probe build only).
+ * None of them changes the arithmetic contract; not thread-safe against concurrent launches. */
+int sfa_tuning_set(const char* name, int32_t value);
 /* Releases the per-device workspaces (synchronises the device). */
 void sfa_release_workspaces(void);
 

@@ -20,7 +20,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 EXPORTED_SYMBOLS = (
     "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
-    "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces",
+    "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces", "sfa_tuning_set",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
     "sfa_peer_close", "sfa_peer_free", "sfa_shard_watchdog",
 )
@@ -152,6 +152,8 @@ def _load() -> C.CDLL:
     lib.sfa_fwd_probe_read.argtypes = [C.POINTER(C.c_uint64), C.c_int32]
     lib.sfa_fwd_probe_read.restype = C.c_int
     lib.sfa_release_workspaces.restype = None
+    lib.sfa_tuning_set.argtypes = [C.c_char_p, C.c_int32]
+    lib.sfa_tuning_set.restype = C.c_int
     lib.sfa_decode_sharded.argtypes = [C.POINTER(DecodeArgs), C.POINTER(ShardComm), C.c_void_p]
     lib.sfa_decode_sharded.restype = C.c_int
     lib.sfa_decode_sharded_emulated.argtypes = [C.POINTER(DecodeArgs), C.c_int32, C.POINTER(C.c_void_p), C.c_uint32, C.c_void_p]

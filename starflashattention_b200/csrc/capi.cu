@@ -108,8 +108,7 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
         return fail(SFA_ERR_INVALID, "rotary cos and sin tables must be given together");
     // One kernel (RoPE + append inside the split-KV kernel) unless SFA_DECODER_FUSED=0 asks for the three-launch
     // form (stand-alone RoPE/append kernel first), kept for A/B checks.
-    const char* fused_env = getenv("SFA_DECODER_FUSED");   // read per call: the GPU tests flip it
-    const bool fused = !(fused_env && atoi(fused_env) == 0);
+    const bool fused = decode_tuning().fused_step != 0;
     const int splits = resolve_splits(a.num_splits, B, H, a.memory_max_len, dev->sm_count);
     const size_t q_bytes = fused ? 0 : align_up((size_t)B * H * D * 2, 256);
     const size_t part_bytes = decode_workspace_bytes(B, H, D, splits);
@@ -410,6 +409,24 @@ int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream) {
     int rc = sfa::check_dtype(dtype);
     if (rc) return rc;
     return sfa::launch_fill(array, value, n, dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sfa_tuning_set(const char* name, int32_t value) {
+    if (!name) return sfa::fail(SFA_ERR_INVALID, "sfa_tuning_set: null name");
+    sfa::DecodeTuning& t = sfa::decode_tuning();
+    const std::string k(name);
+    if (k == "decode_swap") {
+#ifndef SFA_PROBES
+        if (value == 0) return sfa::fail(SFA_ERR_UNSUPPORTED, "decode_swap = 0 exists in the probe build only");
+#endif
+        t.swap = value;
+    } else if (k == "decode_cluster") t.cluster = value;
+    else if (k == "decode_pdl") t.pdl = value;
+    else if (k == "decode_waves") t.waves = value;
+    else if (k == "decode_ctas") t.ctas_per_sm = value;
+    else if (k == "decoder_fused") t.fused_step = value;
+    else return sfa::fail(SFA_ERR_INVALID, "sfa_tuning_set: unknown switch " + k);
+    return SFA_OK;
 }
 
 int sfa_fwd_probe_read(uint64_t* out, int32_t n) {

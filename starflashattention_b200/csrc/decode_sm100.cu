@@ -111,10 +111,14 @@ struct DecodeParams {
     int page_shift;
 };
 
-// Kernel variant (read per call so the GPU tests can flip it): SFA_DECODE_SWAP=0 selects the untransposed MMAs.
+// Kernel variant: decode_tuning().swap == 0 selects the untransposed MMAs, which exist in the -DSFA_PROBES build only
+// (a rejected variant kept for A/B runs: 3 CTAs per SM, zero-padded 16-row query operand).
 inline bool decode_swap_enabled() {
-    const char* e = getenv("SFA_DECODE_SWAP");
-    return e ? atoi(e) != 0 : kDecodeSwapDefault;
+#ifdef SFA_PROBES
+    return decode_tuning().swap != 0;
+#else
+    return true;
+#endif
 }
 
 // Shared memory used only for the end-of-CTA merge of the four warp states.
@@ -159,6 +163,9 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     len = max(0, min(len, p.seqlen_k + p.seqlen_add));   // never read past the cache
     // FUSED: the appended token exists only while the cache has room (as in the stand-alone append kernel)
     const bool has_new = FUSED && pos >= 0 && pos < p.seqlen_k + p.seqlen_add;
+    // row of the rotary tables: they hold seqlen_k + seqlen_add (= memory_max_len) rows; a full cache (pos ==
+    // max_len, nothing is appended) or a garbage length must not index past them
+    const int pos_rope = min(max(pos, 0), p.seqlen_k + p.seqlen_add - 1);
     // Per-sequence chunking keeps ragged batches balanced across the splits.
     const int chunk = (((len + p.num_splits - 1) / p.num_splits) + 63) & ~63;
     const int k_begin = split * chunk;
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
             uint4 w = make_uint4(0, 0, 0, 0);
             if (r < g) {
                 w = *reinterpret_cast<const uint4*>(qrow + 32 * j + 8 * t);
-                if constexpr (FUSED) w = rope_rotate8<T>(w, 32 * j + 8 * t, pos, p.rotary_dim, p.cos_table, p.sin_table);
+                if constexpr (FUSED) w = rope_rotate8<T>(w, 32 * j + 8 * t, pos_rope, p.rotary_dim, p.cos_table, p.sin_table);
             }
             qa[j][0] = w.x; qa[j][1] = w.y; qa[j][2] = w.z; qa[j][3] = w.w;
         }
@@ -236,7 +243,7 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
                 if (from_tok) {
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) {
-                        kf[nt][j] = rope_rotate8<T>(kf[nt][j], 32 * j + 8 * t, pos, p.rotary_dim, p.cos_table, p.sin_table);
+                        kf[nt][j] = rope_rotate8<T>(kf[nt][j], 32 * j + 8 * t, pos_rope, p.rotary_dim, p.cos_table, p.sin_table);
                         if (base + 8 * nt + r == pos)   // the unclamped owner of the row appends it
                             *reinterpret_cast<uint4*>(kcache + (int64_t)(pos - key0) * p.k_rs + 32 * j + 8 * t) = kf[nt][j];
                     }
@@ -490,20 +497,14 @@ __global__ void __launch_bounds__(D * kMergeGroups) decode_combine_kernel(const 
 constexpr int kMaxClusterSplits = 8;
 
 // In-cluster merge (see the CLUSTER note above the kernel): SFA_DECODE_CLUSTER=0 keeps the two-launch form.
-inline bool decode_cluster_enabled() {
-    const char* e = getenv("SFA_DECODE_CLUSTER");
-    return e ? atoi(e) != 0 : true;
-}
+inline bool decode_cluster_enabled() { return decode_tuning().cluster != 0; }
 
 // Programmatic dependent launch (SFA_DECODE_PDL: 0 off, 1 the combine kernel only, 2 = default every decode kernel):
 // a kernel launched this way may be scheduled once the kernel before it on the stream has executed
 // griddepcontrol.launch_dependents in every CTA (ours do so on leaving the streaming loop; a foreign kernel never does,
 // which means "at completion"), and its own griddepcontrol.wait - the first instruction of both kernels - holds it
 // until that kernel has completed and flushed.  Launch latency and CTA start-up move under the predecessor's tail.
-inline int decode_pdl_level() {
-    static const int level = [] { const char* e = getenv("SFA_DECODE_PDL"); return e ? atoi(e) : 2; }();
-    return level;
-}
+inline int decode_pdl_level() { return decode_tuning().pdl; }
 
 template <typename K>
 int launch_ex(K kern, dim3 grid, int threads, size_t smem, int cluster, bool pdl, const DecodeParams& p, cudaStream_t stream) {
@@ -549,8 +550,12 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
         rc = a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, true>, grid, threads, 0, 0, pdl_all, p, stream)
                          : launch_ex(decode_splitkv_kernel<T, D, false, true>, grid, threads, 0, 0, pdl_all, p, stream);
     } else {
+#ifdef SFA_PROBES
         rc = a.fused_qkv ? launch_ex(decode_splitkv_kernel<T, D, true, false>, grid, threads, 0, 0, pdl_all, p, stream)
                          : launch_ex(decode_splitkv_kernel<T, D, false, false>, grid, threads, 0, 0, pdl_all, p, stream);
+#else
+        rc = fail(SFA_ERR_UNSUPPORTED, "the untransposed decode variant exists in the probe build only");
+#endif
     }
     if (rc) return rc;
     if (a.num_splits > 1 && !a.force_partials)
@@ -568,15 +573,25 @@ int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stre
 // a short cache (launch-latency bound): up to 8 cluster splits of at least 128 keys.  (3) Otherwise (few units, long
 // cache) the two-launch form: one wave when that is at most 24 splits, else `waves` rounds of 3 CTAs per SM, chunks
 // of at least 256 keys, at most 256 splits.
-int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
-    static int waves = [] {
-        const char* e = getenv("SFA_DECODE_WAVES");
-        int w = e ? atoi(e) : 0;
-        return w > 0 ? w : 4;
+DecodeTuning& decode_tuning() {
+    static DecodeTuning t = [] {
+        DecodeTuning v;
+        auto geti = [](const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; };
+        v.swap = geti("SFA_DECODE_SWAP", v.swap);
+        v.cluster = geti("SFA_DECODE_CLUSTER", v.cluster);
+        v.pdl = geti("SFA_DECODE_PDL", v.pdl);
+        v.waves = geti("SFA_DECODE_WAVES", v.waves);
+        v.ctas_per_sm = geti("SFA_DECODE_CTAS", v.ctas_per_sm);
+        v.fused_step = geti("SFA_DECODER_FUSED", v.fused_step);
+        return v;
     }();
+    return t;
+}
+
+int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
+    const int waves = decode_tuning().waves > 0 ? decode_tuning().waves : 4;
     const long units = (long)batch * heads_kv;
-    const char* ce = getenv("SFA_DECODE_CTAS");
-    const int ctas_per_sm = ce && atoi(ce) > 0 ? atoi(ce) : 3;
+    const int ctas_per_sm = decode_tuning().ctas_per_sm > 0 ? decode_tuning().ctas_per_sm : 3;
     const long slots = (long)sm_count * ctas_per_sm * waves;
     long s = (slots + units - 1) / units;
     const long max_by_len = max_seqlen / 256 > 0 ? max_seqlen / 256 : 1;

@@ -35,6 +35,19 @@ void* get_workspace(size_t bytes, cudaStream_t stream);
             return ::sfa::fail(SFA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
     } while (0)
 
+// Tuning / A-B switches of the decode path.  Initialised from the environment ONCE per process (SFA_DECODE_SWAP,
+// SFA_DECODE_CLUSTER, SFA_DECODE_PDL, SFA_DECODE_WAVES, SFA_DECODE_CTAS, SFA_DECODER_FUSED); tests and tuning tools
+// change them through sfa_tuning_set().  Nothing on a launch path calls getenv.
+struct DecodeTuning {
+    int swap = 1;        // transposed MMAs (the product form); 0 = untransposed, in the -DSFA_PROBES build only
+    int cluster = 1;     // 2 .. 8 splits merge inside a thread-block cluster; 0 = always partials + combine launch
+    int pdl = 2;         // programmatic dependent launch: 0 off, 1 combine kernel only, 2 every decode kernel
+    int waves = 4;       // rounds of CTAs the two-launch split count aims at
+    int ctas_per_sm = 3;
+    int fused_step = 1;  // decoder step: RoPE + append inside the decode kernel; 0 = stand-alone kernel first
+};
+DecodeTuning& decode_tuning();
+
 // ------------------------------------------------------------------ decode (decode_sm100.cu)
 struct DecodeLaunch {
     const void* q; const void* k; const void* v; const int32_t* seqlens;

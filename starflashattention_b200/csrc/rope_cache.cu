@@ -39,7 +39,7 @@ __global__ void rope_append_kernel(const RopeParams p) {
     const T2 v = *reinterpret_cast<const T2*>(tok + 2 * plane + hd);
     if (2 * i < p.rotary_dim) {
         float c, s;
-        rope_cos_sin<T>(p.cos_table, p.sin_table, pos, i, p.rotary_dim, c, s);
+        rope_cos_sin<T>(p.cos_table, p.sin_table, min(max(pos, 0), p.max_len - 1), i, p.rotary_dim, c, s);   // tables hold max_len rows
         q = make_float2(q.x * c - q.y * s, q.y * c + q.x * s);
         k = make_float2(k.x * c - k.y * s, k.y * c + k.x * s);
     }

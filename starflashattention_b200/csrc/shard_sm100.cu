@@ -119,7 +119,14 @@ __device__ __forceinline__ void shard_exchange_body(const ShardParams& p) {
             }
         }
         __syncthreads();
-        if (!ok_sm) return;
+        if (!ok_sm) {
+            // A peer's row never arrived: the caller must not read an unwritten output as if it were a result.  The
+            // row becomes NaN (O and LSE) and the device flag names the missing rank (sfa_shard_watchdog).
+            T* orow = reinterpret_cast<T*>(p.o) + (int64_t)b * p.o_bs + (int64_t)hq * p.o_hs;
+            if (worker) orow[tid] = (T)__int_as_float(0x7fc00000);
+            if (tid == 0 && p.lse) p.lse[row] = __int_as_float(0x7fc00000);
+            return;
+        }
 #pragma unroll
         for (int r = 0; r < kMaxWorld; ++r)
             src_base[r] = reinterpret_cast<const float*>(p.ws[p.rank] + slot_offset(parity, r < p.world ? r : 0, p.world, p.rows, D));
@@ -175,6 +182,21 @@ template <typename T, int D>
 int launch_mode(const ShardParams& p, int mode, int batch, cudaStream_t stream) {
     dim3 grid(p.heads_q, batch);
     const size_t smem = (size_t)(p.num_splits > 0 ? p.num_splits : 1) * sizeof(float);
+    if (mode == 0) {
+        // A row's block spins until the same row's block of every peer has published: all of a launch's blocks must
+        // be resident at once on every rank (CUDA does not promise in-order dispatch beyond one wave).
+        static int per_sm = [] {
+            int n = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shard_exchange_kernel<T, D, 0>, D * kMergeGroups, 1024) != cudaSuccess) n = 0;
+            return n;
+        }();
+        const DeviceInfo* dev = current_device();
+        if (!dev) return SFA_ERR_NO_DEVICE;
+        if ((long long)p.heads_q * batch > (long long)per_sm * dev->sm_count)
+            return fail(SFA_ERR_UNSUPPORTED, "sharded decode: batch * heads_q = " + std::to_string(p.heads_q * batch) +
+                        " rows exceed one resident wave (" + std::to_string(per_sm * dev->sm_count) +
+                        "); use the publish + all-gather + merge form (mode 1, exchange=\"nccl\")");
+    }
     if (mode == 0) shard_exchange_kernel<T, D, 0><<<grid, D * kMergeGroups, smem, stream>>>(p);
     else if (mode == 1) shard_exchange_kernel<T, D, 1><<<grid, D * kMergeGroups, smem, stream>>>(p);
     else shard_exchange_kernel<T, D, 2><<<grid, D * kMergeGroups, smem, stream>>>(p);

@@ -21,7 +21,7 @@ from . import _capi
 from ._capi import DecodeArgs, DecodePagedArgs, DecoderStepArgs, DecoderStepPagedArgs, FwdArgs, check, lib
 
 __all__ = ["DecoderStepGraph", "fwd", "decode", "fwd_host", "decode_host", "mha_fwd_cuda", "compute_rotary_table", "init_half_array", "fwd_watchdog",
-           "launch_count", "decode_num_splits"]
+           "launch_count", "decode_num_splits", "tuning_set"]
 
 
 def _dtype_code(t: torch.Tensor) -> int:
@@ -365,6 +365,11 @@ def fwd_watchdog(clear: bool = True) -> int:
 
 def launch_count() -> int:
     return int(lib.sfa_launch_count())
+
+
+def tuning_set(name: str, value: int) -> None:
+    """Test / tuning aid: one of the library's A-B switches (see sfa_tuning_set in include/star_flash_attn.h)."""
+    check(lib.sfa_tuning_set(name.encode(), int(value)))
 
 
 # ------------------------------------------------------------------------------------------------

@@ -128,14 +128,18 @@ def local_seqlens(seqlens: torch.Tensor, shard: range) -> torch.Tensor:
 class KVShardedDecode:
     """Split-KV decode of sequences whose KV length is sharded over ``world`` GPUs, one process per GPU.
 
-    ``exchange="peer"``: the merge kernel stores this rank's (O, LSE) rows into every peer's workspace over
+    ``exchange="nccl"`` (default): publish kernel, NCCL ``all_gather_into_tensor``, merge kernel.
+    ``exchange="peer"`` (opt-in): the merge kernel stores this rank's (O, LSE) rows into every peer's workspace over
     NVLink and merges the world's rows in the same launch (CUDA-IPC mapped buffers; ``torch.distributed`` is
-    used once, to hand the 64-byte IPC handles around).  ``exchange="nccl"``: publish kernel, NCCL
-    ``all_gather_into_tensor``, merge kernel - the baseline the fused form is measured against.
+    used once, to hand the 64-byte IPC handles around).  It is the faster form (one launch, no NCCL call), but its
+    blocks spin on the peers' flags: every rank must make the same calls in the same order, ``batch * heads_q``
+    must fit one resident wave (checked by the library), and a peer that never arrives turns the affected rows
+    into NaN after 2 s and latches :meth:`watchdog` - call :meth:`check` at a point where a device synchronise
+    is acceptable; after a failure the instance refuses further steps (the ranks' step counters no longer agree).
     ``peer_ws`` lets a test emulate several ranks inside one process by passing the workspaces directly."""
 
     def __init__(self, batch: int, heads_q: int, heads_kv: int, head_dim: int, shard_len: int, rank: int, world: int,
-                 device, exchange: str = "peer", group=None, peer_ws: Optional[List[int]] = None):
+                 device, exchange: str = "nccl", group=None, peer_ws: Optional[List[int]] = None):
         from . import _capi
         if exchange not in ("peer", "nccl"):
             raise ValueError("exchange must be 'peer' or 'nccl'")
@@ -144,6 +148,7 @@ class KVShardedDecode:
         self.rank, self.world, self.exchange, self.group = rank, world, exchange, group
         self.device = torch.device(device)
         self.step = 0
+        self._failed = 0
         self._owned = None
         self._opened: List[int] = []
         rows = batch * heads_q
@@ -194,6 +199,9 @@ class KVShardedDecode:
         the current stream."""
         from .interface import _decode_args, _stream
         capi = self._capi
+        if self._failed:
+            raise RuntimeError(f"KVShardedDecode: rank {self._failed - 1} did not arrive in an earlier step; the ranks' "
+                               "step counters no longer agree - build a new instance on every rank")
         if out is None:
             out = torch.empty_like(q)
         if lse is None:
@@ -220,7 +228,21 @@ class KVShardedDecode:
         return out, lse
 
     def watchdog(self, clear: bool = True) -> int:
-        return int(self.lib.sfa_shard_watchdog(1 if clear else 0))
+        """Synchronises the device; non-zero (1 + the missing rank) after a peer's rows did not arrive within 2 s."""
+        with torch.cuda.device(self.device):
+            rc = int(self.lib.sfa_shard_watchdog(1 if clear else 0))
+        if rc > 0:
+            self._failed = rc
+        return rc
+
+    def check(self) -> None:
+        """Raises if an exchange timed out since the last check (the affected output rows are NaN)."""
+        rc = self.watchdog()
+        if rc > 0:
+            raise RuntimeError(f"KVShardedDecode: rank {rc - 1}'s rows did not arrive within 2 s; the outputs of that "
+                               "step are NaN")
+        if rc < 0:
+            self._capi.check(rc)
 
     def close(self):
         """Unmaps the peers' buffers and frees the own one (collective: every rank calls it)."""

@@ -53,3 +53,18 @@ def rand_tensor(shape, dtype, seed, scale=1.0):
     import torch
     g = torch.Generator().manual_seed(seed)
     return (torch.randn(shape, generator=g) * scale).to(dtype)
+
+
+@pytest.fixture
+def tuning():
+    """Sets one of the library's A-B switches (sfa_tuning_set) for a test and restores it afterwards:
+    tuning(name, value, default)."""
+    import starflashattention_b200 as sfa
+    undo = []
+
+    def set_(name, value, default):
+        sfa.tuning_set(name, value)
+        undo.append((name, default))
+    yield set_
+    for name, default in undo:
+        sfa.tuning_set(name, default)

@@ -112,3 +112,20 @@ def test_torch_extension_keeps_the_reference_signature(torch_ext):
     t = torch.zeros(1, 3, 1, 128, dtype=torch.float16)
     with pytest.raises(RuntimeError, match="CUDA"):
         torch_ext.mha_fwd_cuda(t, t, t, t, t, t, torch.zeros(1, dtype=torch.int32), t, 1, 8, 1, 128, 128, 8, 1, 0)
+
+
+def test_setup_py_build_ext(tmp_path):
+    """`python setup.py build_ext` (the fixed form of the reference's setup.py:1-30) compiles csrc/flash_api.cpp and
+    links it against libStarFlashAttention.so; the module must import and expose mha_fwd_cuda."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "setup.py", "-q", "build_ext", "--build-lib", str(tmp_path), "--build-temp",
+                        str(tmp_path / "tmp")], cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    built = [f for f in os.listdir(tmp_path) if f.startswith("star_flash_attn") and f.endswith(".so")]
+    assert built, os.listdir(tmp_path)
+    code = ("import sys, torch; sys.path.insert(0, %r); import star_flash_attn as m; "
+            "assert hasattr(m, 'mha_fwd_cuda'); print('ok', m.__file__)" % str(tmp_path))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=str(tmp_path))
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr

@@ -17,8 +17,11 @@ def _rand(shape, dtype, seed):
     return torch.randn(shape, generator=g).to(dtype)
 
 
-def _bound(ref, dtype):
-    return 2e-3 + (0.0 if dtype == torch.float16 else 8e-3) * ref.abs()
+def _bound(mag, dtype):
+    """north_star's 2e-3; bf16 adds the rounding of P (the tensor-core operand) and of O itself, each half an ulp =
+    2^-9 relative, against the oracle's P @ |V| (>= |O|) on the same inputs - the bound of tests/test_fwd_gpu.py.  The
+    cross-rank merge is fp32 and adds nothing at this scale."""
+    return torch.full_like(mag, 2e-3) if dtype == torch.float16 else 2e-3 + 2.0 ** -8 * mag
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
@@ -36,6 +39,7 @@ def test_peer_exchange_matches_oracle(dtype, world, B, Hq, Hkv, D, M, lens):
     vc = _rand((B, M, Hkv, D), dtype, 3)
     seqlens = torch.tensor(lens, dtype=torch.int32)
     o_ref, lse_ref = naive.decode_attention(q, kc, vc, seqlens)
+    mag, _ = naive.decode_attention(q, kc, vc.abs(), seqlens)
     import ctypes as C
     from starflashattention_b200 import _capi
     from starflashattention_b200.interface import _decode_args, _stream
@@ -61,7 +65,7 @@ def test_peer_exchange_matches_oracle(dtype, world, B, Hq, Hkv, D, M, lens):
         assert _capi.lib.sfa_shard_watchdog(1) == 0, "a rank waited more than 2 s for a peer's rows"
         for o, lse in outs:                                 # every rank holds the full result
             err = (o.float().cpu() - o_ref).abs()
-            assert bool((err <= _bound(o_ref, dtype)).all()), float(err.max())
+            assert bool((err <= _bound(mag, dtype)).all()), float(err.max())
             assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
         assert all(torch.equal(outs[0][0], o) for o, _ in outs)
 
@@ -90,7 +94,7 @@ def test_publish_and_merge_form_matches_peer_form():
                                           out.stride(0), out.stride(1), _capi.SFA_BF16, _stream()))
     torch.cuda.synchronize()
     err = (out.float().cpu() - o_ref).abs()
-    assert bool((err <= _bound(o_ref, dtype)).all()), float(err.max())
+    assert bool((err <= _bound(mag, dtype)).all()), float(err.max())
     assert float((lse.cpu() - lse_ref).abs().max()) <= 1e-3
 
 

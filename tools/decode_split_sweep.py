@@ -47,7 +47,7 @@ def main():
         nbytes = 2.0 * B * M * Hkv * D * 2
         auto = sfa.decode_num_splits(B, M, Hkv)
         row = {"auto_splits": auto, "floor_us": nbytes / 6556.8e3}
-        os.environ["SFA_DECODE_CLUSTER"] = "1"
+        sfa.tuning_set("decode_cluster", 1)
         row["auto"] = timed(lambda: sfa.decode(q, kc, vc, sl), flush)
         for s in (1, 2, 4, 6, 8, 9, 10, 12, 14, 16, 18, 24, 32, 48):
             if s * 64 > M and s > 1:
@@ -55,9 +55,9 @@ def main():
             for cl in ("0", "1"):
                 if cl == "1" and not (2 <= s <= 8):
                     continue
-                os.environ["SFA_DECODE_CLUSTER"] = cl
+                sfa.tuning_set("decode_cluster", int(cl))
                 row[f"s{s}" + ("c" if cl == "1" else "")] = timed(lambda: sfa.decode(q, kc, vc, sl, num_splits=s), flush)
-        os.environ["SFA_DECODE_CLUSTER"] = "1"
+        sfa.tuning_set("decode_cluster", 1)
         out[f"B{B}_Hq{Hq}_Hkv{Hkv}_M{M}"] = row
         best = min((v, k) for k, v in row.items() if k.startswith("s"))
         print(f"[split_sweep] B={B} Hq={Hq} Hkv={Hkv} M={M}: floor {row['floor_us']:.1f} us, auto (S={auto}) {row['auto']:.1f} us, "

@@ -47,7 +47,7 @@ def main():
                              rotary_cos_table=cos, rotary_sin_table=sin)
 
     for fused in ("1", "0"):
-        os.environ["SFA_DECODER_FUSED"] = fused
+        sfa.tuning_set("decoder_fused", int(fused))
         for _ in range(3):
             eager()
         n0 = sfa.launch_count()
@@ -55,7 +55,7 @@ def main():
         per = (sfa.launch_count() - n0) // 20
         print(f"[decoder_step] eager fused={fused}: median {med:.1f} us  min {mn:.1f} us  {bytes_step / med / 1e3:.0f} GB/s  "
               f"({per} launches per step, {L} layers)", flush=True)
-    os.environ["SFA_DECODER_FUSED"] = "1"
+    sfa.tuning_set("decoder_fused", 1)
     gr = sfa.DecoderStepGraph(kc, vc, seq, rotary_cos_table=cos, rotary_sin_table=sin)
     gr.qkv.copy_(qkv)
 
