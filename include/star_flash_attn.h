@@ -183,9 +183,16 @@ typedef struct sfa_decoder_step_args {
     int32_t rotary_embedding_dim, qkv_stride, num_layer, idx_layer;
     int32_t num_splits; /* <= 0: launcher's choice */
     int32_t dtype;      /* sfa_dtype; the reference is fp16-only */
+    /* Optional caller-owned device scratch for the split partials (at least sfa_decoder_step_workspace_bytes);
+     * NULL: the library's scratch of this (device, stream), grown outside graph capture only.  A CUDA graph that
+     * captures the step should own its scratch. */
+    void* workspace;
+    size_t workspace_bytes;
 } sfa_decoder_step_args;
 
 int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream);
+/* Scratch the step may need for this shape (an upper bound over the split counts the launcher can choose). */
+size_t sfa_decoder_step_workspace_bytes(int32_t batch_size, int32_t num_heads, int32_t head_dim);
 
 /* ---------------------------------------------------------------- decoder step over a paged cache ---
  * The same fused step (RoPE of q and k at position seq_len[b], append of k, v at row seq_len[b], attention over

@@ -18,7 +18,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_paged",
+    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_workspace_bytes", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces", "sfa_tuning_set",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -98,6 +98,7 @@ class DecoderStepArgs(C.Structure):
         ("head_dim_inv", C.c_float),
         ("rotary_embedding_dim", C.c_int32), ("qkv_stride", C.c_int32), ("num_layer", C.c_int32),
         ("idx_layer", C.c_int32), ("num_splits", C.c_int32), ("dtype", C.c_int32),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
     ]
 
 
@@ -138,6 +139,8 @@ def _load() -> C.CDLL:
     lib.sfa_decode_workspace_bytes.restype = C.c_size_t
     lib.sfa_decoder_step.argtypes = [C.POINTER(DecoderStepArgs), C.c_void_p]
     lib.sfa_decoder_step.restype = C.c_int
+    lib.sfa_decoder_step_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    lib.sfa_decoder_step_workspace_bytes.restype = C.c_size_t
     lib.sfa_decoder_step_paged.argtypes = [C.POINTER(DecoderStepPagedArgs), C.c_void_p]
     lib.sfa_decoder_step_paged.restype = C.c_int
     lib.sfa_rotary_table.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]

@@ -114,8 +114,15 @@ int decoder_step_impl(const sfa_decoder_step_args& a, cudaStream_t stream) {
     const size_t part_bytes = decode_workspace_bytes(B, H, D, splits);
     uint8_t* ws = nullptr;
     if (q_bytes + part_bytes) {
-        ws = reinterpret_cast<uint8_t*>(get_workspace(q_bytes + part_bytes, stream));
-        if (!ws) return SFA_ERR_CUDA;
+        if (a.workspace) {
+            if (a.workspace_bytes < q_bytes + part_bytes)
+                return fail(SFA_ERR_INVALID, "decoder step: workspace too small, need " + std::to_string(q_bytes + part_bytes) + " bytes");
+            if ((uintptr_t)a.workspace % 256) return fail(SFA_ERR_INVALID, "decoder step: workspace must be 256-byte aligned");
+            ws = reinterpret_cast<uint8_t*>(a.workspace);
+        } else {
+            ws = reinterpret_cast<uint8_t*>(get_workspace(q_bytes + part_bytes, stream));
+            if (!ws) return SFA_ERR_CUDA;
+        }
     }
 
     if (!fused) {
@@ -323,6 +330,12 @@ size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_d
 int sfa_decoder_step(const sfa_decoder_step_args* args, void* stream) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decoder_step: null args");
     return sfa::decoder_step_impl(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t sfa_decoder_step_workspace_bytes(int32_t batch_size, int32_t num_heads, int32_t head_dim) {
+    // rotated queries of the three-launch form + partials of the largest split count the launcher can choose
+    const size_t q_bytes = sfa::align_up((size_t)batch_size * num_heads * head_dim * 2, 256);
+    return q_bytes + sfa::decode_workspace_bytes(batch_size, num_heads, head_dim, 256) + 256;
 }
 
 int sfa_decoder_step_paged(const sfa_decoder_step_paged_args* args, void* stream) {

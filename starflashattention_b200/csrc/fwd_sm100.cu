@@ -477,9 +477,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
         };
         uint32_t ring = 0;          // K/V tiles of earlier items
-        uint32_t tiles[NQ];         // key tiles each query tile has been through in earlier items
-#pragma unroll
-        for (int qq = 0; qq < NQ; ++qq) tiles[qq] = 0;
+        // key tiles query tile 0 / the last query tile have been through in earlier items (scalars: an array indexed
+        // by a runtime query-tile number would live in local memory, on the critical path of the score buffer)
+        uint32_t tiles_a = 0, tiles_b = 0;
+        auto tiles_of = [&](int qq) { return qq == 0 ? tiles_a : tiles_b; };
         int q_uses = 0;             // items that loaded Q tile q
         // the last Q.K of the previous non-empty item (the single shared score buffer is handed on across items)
         bool has_last = false;
@@ -525,17 +526,19 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             if (item >= p.total_items) break;
             Item<NQ> it;
             decode_item<NQ>(p, item, it);
-            const int n_q = it.n[q];
+            const int n_q = q == 0 ? it.n[0] : it.n[NQ - 1];   // (no runtime-indexed array: it would live in local memory)
+            SFA_TRACE(tr && n_q > 0, tiles_of(q), q, 7);
             if (n_q > 0) {
                 ok = wait_all(bar_q_full(q), q_uses & 1, 3);
                 ++q_uses;
+                SFA_TRACE(tr, tiles_of(q), q, 4);
             } else {
                 flush_pv();   // an item this warp sits out: nothing to overlap with, and its ring slot must not be held
             }
             for (int j = 0; j < n_q && ok; ++j) {
                 // ---- S(q, j) = Q_q K_j^T
                 const uint32_t gi = ring + 2u * (uint32_t)j, kslot = gi % NSTAGE;
-                const uint32_t t = tiles[q] + (uint32_t)j;      // running tile count of this query tile
+                const uint32_t t = tiles_of(q) + (uint32_t)j;      // running tile count of this query tile
                 int buf = 0;
                 ok = wait_all(bar_kv_full(kslot), (gi / NSTAGE) & 1, 2);
                 SFA_TRACE(tr, t, q, 0);
@@ -545,7 +548,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     if (ord >= 1) {
                         const int prev = tile_of_ordinal(it, ord - 1);
                         const int pq = prev >> 16;
-                        ok = ok && wait_all(bar_s_free(pq), (tiles[pq] + (uint32_t)(prev & 0xffff)) & 1, 9);
+                        ok = ok && wait_all(bar_s_free(pq), (tiles_of(pq) + (uint32_t)(prev & 0xffff)) & 1, 9);
                     } else if (has_last) {
                         ok = ok && wait_all(bar_s_free(last_q), last_parity, 9);
                     }
@@ -588,12 +591,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 if (total > 0) {
                     const int lt = tile_of_ordinal(it, total - 1);
                     last_q = lt >> 16;
-                    last_parity = (tiles[last_q] + (uint32_t)(lt & 0xffff)) & 1;
+                    last_parity = (tiles_of(last_q) + (uint32_t)(lt & 0xffff)) & 1;
                     has_last = true;
                 }
             }
-#pragma unroll
-            for (int qq = 0; qq < NQ; ++qq) tiles[qq] += (uint32_t)it.n[qq];
+            tiles_a += (uint32_t)it.n[0];
+            tiles_b += (uint32_t)it.n[NQ - 1];
             ring += 2u * (uint32_t)it.n_max;
         }
         flush_pv();
@@ -633,9 +636,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             if (item >= p.total_items) break;
             Item<NQ> it;
             decode_item<NQ>(p, item, it);
-            const int n_q = it.n[q];
+            const int n_q = q == 0 ? it.n[0] : it.n[NQ - 1];   // (no runtime-indexed array: it would live in local memory)
             const int row = it.m0 + q * kBlockM + row_in_tile;
             const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
+            SFA_TRACE(tr && n_q > 0, tiles, q, 15);
             float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
             uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
 
@@ -773,7 +777,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 tc_fence_after();
                 if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)(n_q - 1) + 1u, n_q - 1);
             }
-            SFA_STAMP(tr, 26);
+            SFA_TRACE(tr && n_q > 0, tiles + (uint32_t)n_q - 1u, q, 13);
             if (it.m0 + q * kBlockM < p.seqlen_q) {      // uniform over the warpgroup
 #pragma unroll
                 for (int c = 0; c < kSub; ++c) {
@@ -811,7 +815,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     p.lse[((int64_t)it.b * p.heads_q + it.h) * p.seqlen_q + row] = lse;
                 }
             }
-            SFA_STAMP(tr, 27);
+            SFA_TRACE(tr && n_q > 0, tiles + (uint32_t)n_q - 1u, q, 14);
             tiles += (uint32_t)n_q;
             ring += 2u * (uint32_t)it.n_max;
         }

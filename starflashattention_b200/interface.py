@@ -191,10 +191,12 @@ def mha_fwd_cuda(qkv: torch.Tensor, q_bias, k_bias, v_bias, k_cache_table: torch
                  memory_max_len: int, num_heads: int, head_dim: int, rotary_embedding_dim: int,
                  max_input_length: int, num_layer: int, idx_layer: int, *,
                  rotary_cos_table: Optional[torch.Tensor] = None, rotary_sin_table: Optional[torch.Tensor] = None,
-                 lse: Optional[torch.Tensor] = None, num_splits: int = 0) -> torch.Tensor:
+                 lse: Optional[torch.Tensor] = None, num_splits: int = 0,
+                 workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
     """One decoder step: RoPE(q, k) at position seq_len[b], append k, v to layer ``idx_layer`` of the caches,
     attend q over the seq_len[b]+1 cached keys.  Mirrors the reference entry argument for argument
-    (src/flash_api.cpp:42-58); the keyword-only arguments are additions."""
+    (src/flash_api.cpp:42-58); the keyword-only arguments are additions (``workspace``: caller-owned uint8 device
+    scratch of at least ``decoder_step_workspace_bytes`` bytes, instead of the library's per-stream scratch)."""
     dev = _require_cuda(qkv, k_cache_table, v_cache_table, seq_len, o, rotary_cos_table, rotary_sin_table, lse)
     if seq_len.dtype != torch.int32 or not seq_len.is_contiguous() or seq_len.numel() != batch_size:
         raise ValueError("seq_len must be a contiguous int32 tensor of shape (batch_size,)")
@@ -227,9 +229,15 @@ def mha_fwd_cuda(qkv: torch.Tensor, q_bias, k_bias, v_bias, k_cache_table: torch
     a.num_layer, a.idx_layer = num_layer, idx_layer
     a.num_splits = int(num_splits)
     a.dtype = _dtype_code(qkv)
+    if workspace is not None:
+        a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     with torch.cuda.device(dev):
         check(lib.sfa_decoder_step(a, _stream()))
     return o
+
+
+def decoder_step_workspace_bytes(batch_size: int, num_heads: int, head_dim: int) -> int:
+    return int(lib.sfa_decoder_step_workspace_bytes(batch_size, num_heads, head_dim))
 
 
 def decoder_step_paged(qkv: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor,
@@ -306,27 +314,32 @@ class DecoderStepGraph:
         self.o = torch.empty((L, B, H, D), dtype=k_cache_table.dtype, device=dev)
         self.lse = torch.empty((L, B, H), dtype=torch.float32, device=dev)
         rot = D if rotary_embedding_dim is None else rotary_embedding_dim
+        # The graph owns its scratch: the captured launches keep its address for as long as the graph lives, whatever
+        # the library's own per-stream scratch does in the meantime.
+        self.workspace = torch.empty(decoder_step_workspace_bytes(B, H, D), dtype=torch.uint8, device=dev)
 
         def run():
             for layer in range(L):
                 mha_fwd_cuda(self.qkv[layer], None, None, None, k_cache_table, v_cache_table, self.seq_len,
                              self.o[layer], B, M, H, D, rot, M, L, layer, rotary_cos_table=rotary_cos_table,
-                             rotary_sin_table=rotary_sin_table, lse=self.lse[layer], num_splits=num_splits)
+                             rotary_sin_table=rotary_sin_table, lse=self.lse[layer], num_splits=num_splits,
+                             workspace=self.workspace)
             self.seq_len.add_(1)
 
-        # Warm up on a side stream (grows the library's workspace outside capture), then roll the state back.
+        # Warm up on a side stream, then roll the state back.
         k0, v0, s0 = k_cache_table.clone(), v_cache_table.clone(), self.seq_len.clone()
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
+        n0 = launch_count()
         with torch.cuda.stream(side):
             run()
+        self.launches_per_step = launch_count() - n0        # kernels of this library in one step
         torch.cuda.current_stream(dev).wait_stream(side)
         k_cache_table.copy_(k0); v_cache_table.copy_(v0); self.seq_len.copy_(s0)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             run()
         k_cache_table.copy_(k0); v_cache_table.copy_(v0); self.seq_len.copy_(s0)
-        self.launches_per_step = L * (2 if decode_num_splits(B, M, H, dev) > 1 or num_splits > 1 else 1)
 
     def step(self, qkv: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Replays the captured step on the current stream; returns the static output tensor."""

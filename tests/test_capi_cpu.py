@@ -42,7 +42,9 @@ def test_abi_version_and_struct_sizes(built_library):
     assert ctypes.sizeof(_capi.FwdArgs) == 5 * 8 + 6 * 4 + 12 * 8 + 4 + 2 * 4 + 4
     assert ctypes.sizeof(_capi.DecodeArgs) == 6 * 8 + 5 * 4 + 4 + 10 * 8 + 3 * 4 + 4 + 8 + 8
     assert ctypes.sizeof(_capi.DecodePagedArgs) == ctypes.sizeof(_capi.DecodeArgs) + 8 + 8 + 4 + 4
-    assert ctypes.sizeof(_capi.DecoderStepArgs) == 8 * 8 + 4 * 4 + 4 + 6 * 4 + 4
+    assert ctypes.sizeof(_capi.DecoderStepArgs) == 8 * 8 + 4 * 4 + 4 + 6 * 4 + 4 + 8 + 8     # + workspace, workspace_bytes
+    assert ctypes.sizeof(_capi.FwdHostArgs) == ctypes.sizeof(_capi.FwdArgs) + 8
+    assert ctypes.sizeof(_capi.DecodeHostArgs) == ctypes.sizeof(_capi.DecodeArgs) + 8
 
 
 def test_argument_validation_without_gpu(built_library):

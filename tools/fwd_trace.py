@@ -1,7 +1,9 @@
-"""Event trace of one CTA of the prefill kernel (SFA_FWD_DBG=6): where the MMA warp and the softmax warpgroups
-wait for each other.  Prints clock64() times relative to the first event of the window.
+"""Event trace of CTA 0 of the persistent prefill kernel (probe build: python starflashattention_b200/build.py --probes):
+where the MMA warps and the softmax warpgroups wait for each other, in steady state and across an item boundary.
+Prints clock64() times relative to the first event of the window; tiles are numbered by the running count of key
+tiles the CTA has processed for a query tile (CTA 0 starts with the heaviest item: 63 / 64 tiles at N = 8192).
 
-    SFA_FWD_DBG=6 python tools/fwd_trace.py [first_tile] [tiles]
+    SFA_PROBES_LIB=1 python tools/fwd_trace.py [first_tile] [tiles]
 """
 import ctypes
 import os
@@ -10,16 +12,15 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
-os.environ.setdefault("SFA_FWD_DBG", "6")
+os.environ["SFA_PROBES_LIB"] = "1"
 import starflashattention_b200 as sfa  # noqa: E402
 from starflashattention_b200 import _capi  # noqa: E402
 
-NAMES = {7: "mma: QK step start", 0: "mma: K tile and S buffer acquired", 1: "mma: commits flushed, QK issue",
-         13: "mma: QK 8 MMAs accepted", 14: "mma: V tile acquired", 2: "mma: P half 0 acquired",
-         3: "mma: commits flushed, PVa issue", 4: "mma: PVa issued", 5: "mma: P half 1 acquired, PVb issue",
-         15: "mma: PVb 4 MMAs accepted",
-         8: "wg : S seen", 9: "wg : S-free arrive", 10: "wg : exp start", 11: "wg : P half 0 arrive",
-         12: "wg : P half 1 arrive"}
+NAMES = {7: "mma: item start", 4: "mma: Q tile acquired", 0: "mma: K tile acquired", 1: "mma: S buffer acquired, QK issue",
+         2: "mma: QK issued + committed", 3: "mma: V tile, P half 0 acquired, PVa issue", 5: "mma: P half 1 acquired, PVb issue",
+         6: "mma: PVb issued + committed",
+         15: "wg : item start", 8: "wg : S seen", 9: "wg : S-free arrive", 10: "wg : exp start", 11: "wg : P half 0 arrive",
+         12: "wg : P half 1 arrive", 13: "wg : last P.V of the item seen (epilogue start)", 14: "wg : O stored (TMA store issued), LSE written"}
 
 
 def main():
@@ -31,33 +32,38 @@ def main():
     for _ in range(2):
         sfa.fwd(q, k, v, causal=True)
     torch.cuda.synchronize()
-    n = 32 + 2048
+    n = 32 + 4096
     buf = (ctypes.c_uint64 * n)()
-    _capi.lib.sfa_fwd_probe_read(buf, n)
-    ev = []
-    for j in range(j0, j0 + nj):
-        for qq in (0, 1):
-            for e, name in NAMES.items():
-                t = buf[32 + (j * 2 + qq) * 16 + e]
-                if t:
-                    ev.append((t, f"q{qq} j{j} {name}"))
-    ev.sort()
-    t0 = ev[0][0]
-    for t, name in ev:
-        print(f"{t - t0:7d}  {name}")
-    # prologue / epilogue of the CTA (the heaviest query block: 64 key tiles per query tile)
-    t_in, t_setup, t_lastpv, t_stored, t_out = (buf[i] for i in (24, 25, 26, 27, 28))
-    first_qk = buf[32 + 1]                          # q0 j0 "commits flushed, QK issue"
-    first_s = buf[32 + 8]                           # q0 j0 "S seen"
+    _capi.check(_capi.lib.sfa_fwd_probe_read(buf, n))
+
+    def window(lo, hi, title):
+        ev = []
+        for j in range(lo, hi):
+            for qq in (0, 1):
+                for e, name in NAMES.items():
+                    t = buf[32 + (j * 2 + qq) * 16 + e]
+                    if t:
+                        ev.append((t, f"q{qq} t{j} {name}"))
+        ev.sort()
+        if not ev:
+            return
+        print(f"---- {title}")
+        t0 = ev[0][0]
+        for t, name in ev:
+            print(f"{t - t0:7d}  {name}")
+    window(j0, j0 + nj, f"steady state, tiles {j0} .. {j0 + nj - 1}")
+    window(61, 67, "item boundary of CTA 0 (first item: 63 / 64 tiles)")
+    t_in, t_setup, t_out = (buf[i] for i in (24, 25, 28))
     if t_in and t_out:
-        print(f"CTA (0,0,0): {t_out - t_in} cycles in all; entry -> set-up done {t_setup - t_in}, -> first QK issue "
-              f"{first_qk - t_in}, -> first S seen {first_s - t_in}; last P.V seen -> O stored {t_stored - t_lastpv}, "
-              f"-> exit {t_out - t_lastpv}")
-    # per-tile periods
+        print(f"CTA 0: {t_out - t_in} cycles in all; entry -> set-up done {t_setup - t_in}")
     for qq in (0, 1):
         ts = [buf[32 + (j * 2 + qq) * 16 + 8] for j in range(8, 60)]
         d = [b - a for a, b in zip(ts, ts[1:])]
         print(f"q{qq}: mean cycles between consecutive 'S seen' (tiles 8..59): {sum(d) / len(d):.0f}")
+        ts = [buf[32 + (j * 2 + qq) * 16 + 8] for j in range(70, 120)]
+        d = [b - a for a, b in zip(ts, ts[1:]) if a and b]
+        if d:
+            print(f"q{qq}: mean cycles between consecutive 'S seen' (tiles 70..119, later items): {sum(d) / len(d):.0f}")
 
 
 if __name__ == "__main__":
