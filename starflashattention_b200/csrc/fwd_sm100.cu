@@ -77,18 +77,17 @@ __device__ unsigned long long g_fwd_probe[32 + 4096];
 #define SFA_STAMP(cond, i) do { } while (0)
 #endif
 
-// Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.
+// Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.  The bound is a count of
+// failed try_waits (each suspends the thread for a hardware time slice), not a clock: this code is inlined at every
+// wait of the kernel, and the %globaltimer version made up a third of its instructions (instruction cache).
+constexpr uint32_t kMaxWaitSpins = 1u << 24;
 __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
     if (mbar_try_wait(bar, parity)) return true;
-    const uint64_t t0 = global_timer_ns();
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if ((++spins & 0xFF) == 0) {
-            if (*(volatile int*)error_flag != 0) return false;
-            if (global_timer_ns() - t0 > 2000000000ull) {
-                atomicCAS(error_flag, 0, code);
-                return false;
-            }
+        if (++spins >= kMaxWaitSpins || ((spins & 0xFFF) == 0 && *(volatile int*)error_flag != 0)) {
+            atomicCAS(error_flag, 0, code);
+            return false;
         }
     }
     return true;
@@ -170,12 +169,12 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
     }
 }
 
-// Register split between the softmax warpgroups and the warpgroup holding the TMA / MMA warps (NQ == 2 only).
+// Register split between the softmax warpgroups and the warpgroup holding the producer / issuer warps.
 // setmaxnreg.inc blocks until the CTA's own pool (registers per thread at launch x threads) can cover the
 // request, so the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
 template <int NQ>
 struct FwdRegs {
-    static constexpr int kThreads = NQ * 128 + (NQ == 2 ? 128 : 64);
+    static constexpr int kThreads = NQ * 128 + 128;   // softmax warpgroups + one warpgroup of four single-purpose warps
     static constexpr bool kSet = NQ == 2;
     // registers ptxas may use at launch: floor(65536 / threads) rounded down to a multiple of 8
     static constexpr int kLaunch = (65536 / kThreads) / 8 * 8;
@@ -203,6 +202,7 @@ struct FwdTmem {
 
 template <int D, int NQ, int NSTAGE>
 struct FwdSmem {
+    static_assert(NSTAGE % 2 == 0, "K tiles live in the even ring slots, V tiles in the odd ones");
     static constexpr int kSubTileBytes = kBlockM * 128;              // 128 rows x 64 elements x 2 B
     static constexpr int kTileBytes = (D / 64) * kSubTileBytes;      // one 128 x D tile
     static constexpr int kQOff = 0;
@@ -213,23 +213,26 @@ struct FwdSmem {
     // barriers: q_full[NQ], q_empty[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], pv_done[NQ],
     //           s_free[2], sched_full[2], sched_empty[2]
     static constexpr int kNumBars = 6 * NQ + 2 * NSTAGE + 6;
-    static constexpr int kSchedOff = kBarOff + kNumBars * 8;         // two published item indices
-    static constexpr int kTmemPtrOff = kSchedOff + 16;
+    static constexpr int kSchedOff = (kBarOff + kNumBars * 8 + 15) / 16 * 16;   // two published work items, 32 B each
+    static constexpr int kTmemPtrOff = kSchedOff + 64;
     static constexpr int kBytes = kTmemPtrOff + 16;
     static constexpr int kAlloc = kBytes + 1024;                     // slack for the 1024 B alignment
     static_assert(kAlloc <= 232448, "shared memory budget exceeded");
 };
 
-// One work item: NQ query tiles of one (batch, head).
-template <int NQ>
+// One work item as the scheduler warp publishes it: two query tiles (n1, and everything about query tile 1, is
+// unused with one query tile per CTA) of one (batch, head).
 struct Item {
-    int m0, h, b, hk;
-    int n[NQ];      // key tiles each query tile needs (causal: up to the diagonal of its last row)
+    int m0, h, b, hk;   // first query row, query head, batch entry, kv head
+    int n0, n1;         // key tiles query tile 0 / 1 needs (causal: up to the diagonal of its last row)
     int n_max;
+    int index;          // >= total_items: the end of the schedule
 };
 
 template <int NQ>
-__device__ __forceinline__ void decode_item(const FwdParams& p, int idx, Item<NQ>& it) {
+__device__ __forceinline__ Item decode_item(const FwdParams& p, int idx) {
+    Item it;
+    it.index = idx;
     const int per_group = p.group_heads * p.m_blocks;
     const int g = idx / per_group;
     const int r = idx - g * per_group;
@@ -244,25 +247,26 @@ __device__ __forceinline__ void decode_item(const FwdParams& p, int idx, Item<NQ
     it.m0 = m_block * (NQ * kBlockM);
     const int kv_tiles_total = (p.seqlen_k + kBlockN - 1) / kBlockN;
     const int causal_shift = p.seqlen_k - p.seqlen_q;   // query i sees keys <= i + shift
-    it.n_max = 0;
+    int n[2] = {0, 0};
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-        int n = kv_tiles_total;
+        int t = kv_tiles_total;
         if (p.causal) {
             const int last_row = min(it.m0 + (q + 1) * kBlockM, p.seqlen_q) - 1;
             const int last_key = last_row + causal_shift;
-            n = last_key < 0 ? 0 : min(kv_tiles_total, last_key / kBlockN + 1);
+            t = last_key < 0 ? 0 : min(kv_tiles_total, last_key / kBlockN + 1);
         }
-        if (it.m0 + q * kBlockM >= p.seqlen_q) n = 0;   // tile entirely past the end of Q
-        it.n[q] = n;
-        it.n_max = max(it.n_max, n);
+        if (it.m0 + q * kBlockM >= p.seqlen_q) t = 0;   // tile entirely past the end of Q
+        n[q] = t;
     }
+    it.n0 = n[0];
+    it.n1 = n[1];
+    it.n_max = max(n[0], n[1]);
+    return it;
 }
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-// SOFTREL: ring slots are handed back by the softmax warpgroups (plain arrive once they have seen the
-// MMA's completion barrier) instead of by two more tcgen05.commit per tile from the MMA warps.
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, bool SOFTREL>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY>
 __global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const __grid_constant__ CUtensorMap o_map, const FwdParams p) {
@@ -271,9 +275,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     using T = FwdTmem<D, NQ>;
     constexpr bool kSetRegs = R::kSet;
     constexpr int kSoftmaxWarps = 4 * NQ;
+    constexpr int kWarpKV = kSoftmaxWarps, kWarpQK = kSoftmaxWarps + 1, kWarpPV = kSoftmaxWarps + 2, kWarpSched = kSoftmaxWarps + 3;
     constexpr int kSBufs = T::kSBufs;
     constexpr int kSub = D / 64;
-    constexpr int kSchedConsumers = 5 * NQ;   // softmax warps + MMA warps
+    constexpr int kSchedConsumers = 4 * NQ + 3;   // softmax warps + K/V producer + the two issuer warps
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -282,10 +287,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     auto bar_q_full = [&](int q) { return bar_base + 8u * q; };
     // every Q.K of the item that reads Q tile q has completed: the tile may be overwritten by the next item's
     auto bar_q_empty = [&](int q) { return bar_base + 8u * (NQ + q); };
-    auto bar_kv_full = [&](int s) { return bar_base + 8u * (2 * NQ + s); };
-    auto bar_kv_empty = [&](int s) { return bar_base + 8u * (2 * NQ + NSTAGE + s); };
+    auto bar_kv_full = [&](uint32_t s) { return bar_base + 8u * (2 * NQ + s); };
+    auto bar_kv_empty = [&](uint32_t s) { return bar_base + 8u * (2 * NQ + NSTAGE + s); };
     auto bar_s_full = [&](int q) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + q); };
-    // P is handed to the MMA warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
+    // P is handed to the P.V warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
     auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (3 * NQ + 2 * NSTAGE + 2 * q + half); };
     // every P.V of query tile q has completed: P(q) may be overwritten, O(q) may be rescaled / read
     auto bar_pv_done = [&](int q) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + q); };
@@ -293,7 +298,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     auto bar_s_free = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + i); };
     auto bar_sched_full = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 2 + i); };
     auto bar_sched_empty = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 4 + i); };
-    volatile int* sched_slot = reinterpret_cast<volatile int*>(smem_gen + L::kSchedOff);
+    volatile int4* sched_slot = reinterpret_cast<volatile int4*>(smem_gen + L::kSchedOff);   // [2 * entry], [2 * entry + 1]
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -303,7 +308,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
 #endif
     SFA_STAMP(trace_cta && threadIdx.x == 0, 24);
 
-    if (warp == kSoftmaxWarps && lane == 0) {
+    if (warp == kWarpKV && lane == 0) {
         prefetch_tensormap(&q_map);
         prefetch_tensormap(&k_map);
         prefetch_tensormap(&v_map);
@@ -326,11 +331,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
 #pragma unroll
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bar_kv_full(s), 1);
-            mbar_init(bar_kv_empty(s), NQ);   // one arrival per query tile
+            mbar_init(bar_kv_empty(s), 1);   // one commit behind the last Q.K (K slots) / P.V (V slots) that reads the tile
         }
         fence_barrier_init();
     }
-    if (warp == kSoftmaxWarps + 1) {
+    if (warp == kWarpQK) {
         tmem_alloc(smem_base + L::kTmemPtrOff, T::kCols);
         tmem_relinquish();
     }
@@ -340,64 +345,58 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     const uint32_t tmem_base = *tmem_ptr_smem;
     SFA_STAMP(trace_cta && threadIdx.x == 0, 25);
 
-    // Q.K products of an item are ordered j-major, q-minor; the k-th one writes score buffer k % kSBufs.
-    auto qk_ordinal = [&](const Item<NQ>& it, int q, int j) {
-        int k = 0;
-#pragma unroll
-        for (int qq = 0; qq < NQ; ++qq) k += min(j, it.n[qq]) + ((qq < q && j < it.n[qq]) ? 1 : 0);
-        return k;
-    };
-    // inverse of qk_ordinal (two query tiles): (query tile << 16) | key tile
-    auto tile_of_ordinal = [&](const Item<NQ>& it, int ord) {
-        const int n0 = it.n[0], n1 = it.n[NQ - 1], m = min(n0, n1);
-        if (ord < 2 * m) return ((ord & 1) << 16) | (ord >> 1);
-        return ((n0 > n1 ? 0 : 1) << 16) | (m + ord - 2 * m);
-    };
-    // how many query tiles of the item read key tile j
-    auto users = [&](const Item<NQ>& it, int j) {
-        int u = 0;
-#pragma unroll
-        for (int qq = 0; qq < NQ; ++qq) u += j < it.n[qq] ? 1 : 0;
-        return u;
-    };
     // Consumer side of the schedule: the k-th item of this CTA (index >= total_items ends the loop).
     auto next_item = [&](int k, bool& ok) {
         ok = __all_sync(0xffffffffu, wait_barrier(bar_sched_full(k & 1), (k >> 1) & 1, p.error_flag, 12)) != 0;
-        const int item = sched_slot[k & 1];
+        const int4 a = const_cast<const int4&>(reinterpret_cast<const volatile int4&>(sched_slot[2 * (k & 1)]));
+        const int4 b = const_cast<const int4&>(reinterpret_cast<const volatile int4&>(sched_slot[2 * (k & 1) + 1]));
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_sched_empty(k & 1));
-        return ok ? item : INT_MAX;
+        Item it;
+        it.m0 = a.x; it.h = a.y; it.b = a.z; it.hk = a.w;
+        it.n0 = b.x; it.n1 = b.y; it.n_max = b.z; it.index = ok ? b.w : INT_MAX;
+        return it;
+    };
+    auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
+        return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
     };
 
-    // NQ == 2 runs three full warpgroups (the third holds the TMA and MMA warps plus one idle
-    // warp) so the register file can be re-split: the softmax warpgroups take what the others give up.
-    if (warp == kSoftmaxWarps) {
-        // =============================================================== scheduler + TMA producer
+    // Four single-purpose warps beside the softmax warpgroups; with two query tiles they form a third warpgroup so the
+    // register file can be re-split: the softmax warpgroups take what these give up.
+    if (warp == kWarpSched) {
+        // =============================================================== scheduler + Q producer
+        // Fetches the next item one item ahead (atomicAdd; the first one is static), decodes it and publishes it
+        // to every other warp; loads the item's Q tiles as soon as the previous item's last Q.K has released them -
+        // a warp of its own, so a Q load never queues behind the K/V ring's waits.
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
-        // whole warp in the loop (uniform control flow), one elected lane issues
-        int item = blockIdx.x;      // the first item is static, the later ones come from the counter
-        uint32_t ring = 0;          // K/V tiles loaded so far (all items)
-        int q_loads[NQ];            // Q tiles loaded so far, per query tile
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) q_loads[q] = 0;
+        int item = blockIdx.x;
+        int q_loads0 = 0, q_loads1 = 0;   // Q tiles loaded so far, per query tile
         bool ok = true;
         for (int k = 0; ok; ++k) {
-            if (k >= 2) ok = __all_sync(0xffffffffu, wait_barrier(bar_sched_empty(k & 1), ((k >> 1) - 1) & 1, p.error_flag, 13)) != 0;
+            if (k >= 2) ok = wait_all(bar_sched_empty(k & 1), ((k >> 1) - 1) & 1, 13);
             if (!ok) break;
+            Item it;
+            it.index = item;
+            if (item < p.total_items) it = decode_item<NQ>(p, item);
             if (lane == 0) {
-                sched_slot[k & 1] = item;
+                if (item < p.total_items) {
+                    const_cast<int4&>(reinterpret_cast<volatile int4&>(sched_slot[2 * (k & 1)])) = make_int4(it.m0, it.h, it.b, it.hk);
+                    const_cast<int4&>(reinterpret_cast<volatile int4&>(sched_slot[2 * (k & 1) + 1])) = make_int4(it.n0, it.n1, it.n_max, item);
+                } else {
+                    const_cast<int4&>(reinterpret_cast<volatile int4&>(sched_slot[2 * (k & 1) + 1])) = make_int4(0, 0, 0, INT_MAX);
+                }
                 mbar_arrive(bar_sched_full(k & 1));
             }
             __syncwarp();
             if (item >= p.total_items) break;
             int nxt = 0;
             if (lane == 0) nxt = (int)gridDim.x + atomicAdd(p.sched, 1);   // used one item later: its latency is hidden
-            Item<NQ> it;
-            decode_item<NQ>(p, item, it);
-            auto load_q = [&](int q) {
-                if (it.n[q] == 0) return;
-                if (q_loads[q] >= 1)
-                    ok = ok && __all_sync(0xffffffffu, wait_barrier(bar_q_empty(q), (q_loads[q] - 1) & 1, p.error_flag, 11)) != 0;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int n_q = q == 0 ? it.n0 : it.n1;
+                if (n_q == 0) continue;
+                const int loads = q == 0 ? q_loads0 : q_loads1;
+                if (loads >= 1) ok = ok && wait_all(bar_q_empty(q), (loads - 1) & 1, 11);
                 if (ok && elect_one()) {
                     mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
 #pragma unroll
@@ -406,12 +405,29 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                                     64 * s, it.h, it.m0 + q * kBlockM, it.b);
                 }
                 __syncwarp();
-                ++q_loads[q];
-            };
-            auto load_kv = [&](int i) {   // i-th K/V tile of the item: K_0 V_0 K_1 V_1 ...
+                if (q == 0) ++q_loads0; else ++q_loads1;
+            }
+            item = __shfl_sync(0xffffffffu, nxt, 0);
+        }
+        // Last CTA out rezeroes the schedule counters for the next launch that uses this slot.
+        if (lane == 0) {
+            __threadfence();
+            const unsigned old = atomicInc(reinterpret_cast<unsigned*>(p.sched + 1), gridDim.x - 1);
+            if (old == gridDim.x - 1) p.sched[0] = 0;
+        }
+    } else if (warp == kWarpKV) {
+        // =============================================================== K/V producer
+        // K_0 V_0 K_1 V_1 ... of every item through one ring that runs on across items (K in the even slots, V in
+        // the odd ones): the next item's first tiles arrive under the current item's last P.V and epilogue.
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
+        uint32_t ring = 0;          // K/V tiles loaded so far (all items)
+        bool ok = true;
+        for (int k = 0; ok; ++k) {
+            const Item it = next_item(k, ok);
+            if (it.index >= p.total_items) break;
+            for (int i = 0; i < 2 * it.n_max && ok; ++i) {
                 const uint32_t gi = ring + (uint32_t)i, slot = gi % NSTAGE, use = gi / NSTAGE;
-                if (use >= 1)
-                    ok = ok && __all_sync(0xffffffffu, wait_barrier(bar_kv_empty(slot), (use - 1) & 1, p.error_flag, 1)) != 0;
+                if (use >= 1) ok = wait_all(bar_kv_empty(slot), (use - 1) & 1, 1);
                 if (ok && elect_one()) {
                     mbar_arrive_expect_tx(bar_kv_full(slot), L::kTileBytes);
                     const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
@@ -421,193 +437,147 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                                     bar_kv_full(slot), 64 * s, it.hk, (i >> 1) * kBlockN, it.b);
                 }
                 __syncwarp();
-            };
-            // Q0, K0 first: the item's first Q.K needs exactly those two
-            load_q(0);
-            if (it.n_max > 0) load_kv(0);
-#pragma unroll
-            for (int q = 1; q < NQ; ++q) load_q(q);
-            for (int i = 1; i < 2 * it.n_max && ok; ++i) load_kv(i);
+            }
             ring += 2u * (uint32_t)it.n_max;
-            item = __shfl_sync(0xffffffffu, nxt, 0);
         }
-        // Last CTA out rezeroes the schedule counters for the next launch that uses this slot.
-        if (lane == 0) {
-            __threadfence();
-            const unsigned old = atomicInc(reinterpret_cast<unsigned*>(p.sched + 1), gridDim.x - 1);
-            if (old == gridDim.x - 1) p.sched[0] = 0;
-        }
-    } else if (warp > kSoftmaxWarps && warp <= kSoftmaxWarps + NQ) {
-        // =============================================================== tcgen05 issuers, one warp per query tile
+    } else if (warp == kWarpQK) {
+        // =============================================================== Q.K issuer: S(q, j) = Q_q K_j^T for both query tiles
+        // Order: key tile major, query tile minor - the order in which the softmax warpgroups hand the score buffer
+        // back.  This warp does nothing else, so it is parked on the buffer's barrier when the hand-back comes: the
+        // turnaround of the single score buffer (head_dim 128) is the critical cycle of the kernel.
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         // The whole warp runs the loop (uniform control flow keeps descriptors in uniform registers); one elected
         // lane issues.  Descriptors are built once per operand tile and advanced by compile-time constants.
         constexpr uint32_t idesc_qk = mma_idesc(BF16, 0, 0, kBlockM, kBlockN);
-        constexpr uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
-        // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.  V: MN-major (head_dim
-        // contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
+        // Q, K: K-major, rows of 128 B, 8-row groups 1024 B apart.
         constexpr uint64_t desc_kmajor = smem_desc_sw128(16, 1024);
-        constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
         const uint64_t ring_k_desc = smem_desc_at(desc_kmajor, smem_base + L::kRingOff);
-        const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
+        const uint64_t q_desc0 = smem_desc_at(desc_kmajor, smem_base + L::kQOff);
         bool ok = true;
-        const int q = NQ == 1 ? 0 : warp - (kSoftmaxWarps + 1);   // the query tile this warp issues for
-        const uint64_t q_desc = smem_desc_at(desc_kmajor, smem_base + L::kQOff + q * L::kTileBytes);
-        // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
-        auto issue_qk = [&](uint32_t slot, int buf) {
-            const uint64_t k_desc = ring_k_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
-            const uint32_t s_tmem = tmem_base + T::kSOff + buf * kBlockN;
-#pragma unroll
-            for (int kc = 0; kc < D / 16; ++kc) {
-                const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
-                mma_ss(s_tmem, q_desc + off16, k_desc + off16, idesc_qk, kc > 0);
-            }
-        };
-        auto issue_pv = [&](uint32_t slot, int half, bool accumulate) {   // keys [64 * half, 64 * half + 64)
-            const uint64_t v_desc = ring_v_desc + (uint64_t)(slot * (L::kTileBytes >> 4));
-            const uint32_t p_tmem = tmem_base + T::kPOff + q * (kBlockN / 2);
-            const uint32_t o_tmem = tmem_base + T::kOOff + q * D;
-#pragma unroll
-            for (int kk = 0; kk < kBlockN / 32; ++kk) {
-                const int kc = half * (kBlockN / 32) + kk;
-                mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, accumulate || kc > 0);
-            }
-        };
-        auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
-            return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
-        };
-        uint32_t ring = 0;          // K/V tiles of earlier items
-        // key tiles query tile 0 / the last query tile have been through in earlier items (scalars: an array indexed
-        // by a runtime query-tile number would live in local memory, on the critical path of the score buffer)
-        uint32_t tiles_a = 0, tiles_b = 0;
-        auto tiles_of = [&](int qq) { return qq == 0 ? tiles_a : tiles_b; };
-        int q_uses = 0;             // items that loaded Q tile q
-        // the last Q.K of the previous non-empty item (the single shared score buffer is handed on across items)
-        bool has_last = false;
-        int last_q = 0;
-        uint32_t last_parity = 0;
+        uint32_t ring = 0;                  // K/V tiles of earlier items
+        uint32_t tiles0 = 0, tiles1 = 0;    // key tiles each query tile has been through in earlier items
+        int q_uses0 = 0, q_uses1 = 0;       // items that loaded Q tile 0 / 1
+        // the Q.K issued last (any item): its warpgroup hands the shared score buffer on
+        bool has_prev = false;
+        int prev_q = 0;
+        uint32_t prev_t = 0;
 #ifdef SFA_PROBES
         const bool tr = trace_cta && lane == 0;
 #endif
-        // O(q) += P V of the tile whose Q.K was issued last; it is issued BEHIND the next tile's Q.K - also across an
-        // item boundary, so the scores of an item's first tile are on their way while the warpgroup still works on
-        // the previous item's last tile and epilogue.
-        struct Pending {
-            bool valid;
-            uint32_t gi;        // ring index of the tile's V
-            uint32_t t;         // running tile count (parity of p_ready)
-            bool accumulate;    // false for the first key tile of an item
-            int releases;       // arrivals on the ring slot this warp owes (its own plus absent query tiles')
-        } pend = {false, 0u, 0u, false, 0};
-        auto flush_pv = [&]() {   // in two halves of 64 keys
-            if (!pend.valid) return;
-            pend.valid = false;
-            const uint32_t vslot = pend.gi % NSTAGE;
-            ok = ok && wait_all(bar_kv_full(vslot), (pend.gi / NSTAGE) & 1, 4);
-            ok = ok && wait_all(bar_p_ready(q, 0), pend.t & 1, 5);
-            tc_fence_after();
-            SFA_TRACE(tr, pend.t, q, 3);
-            if (ok && elect_one()) issue_pv(vslot, 0, pend.accumulate);
-            __syncwarp();
-            ok = ok && wait_all(bar_p_ready(q, 1), pend.t & 1, 5);
-            tc_fence_after();
-            SFA_TRACE(tr, pend.t, q, 5);
-            if (ok && elect_one()) {
-                issue_pv(vslot, 1, true);
-                tc_commit(bar_pv_done(q));
-                if constexpr (!SOFTREL)
-                    for (int u = 0; u < pend.releases; ++u) tc_commit(bar_kv_empty(vslot));
-            }
-            __syncwarp();
-            SFA_TRACE(tr, pend.t, q, 6);
-        };
         for (int k = 0; ok; ++k) {
-            const int item = next_item(k, ok);
-            if (item >= p.total_items) break;
-            Item<NQ> it;
-            decode_item<NQ>(p, item, it);
-            const int n_q = q == 0 ? it.n[0] : it.n[NQ - 1];   // (no runtime-indexed array: it would live in local memory)
-            SFA_TRACE(tr && n_q > 0, tiles_of(q), q, 7);
-            if (n_q > 0) {
-                ok = wait_all(bar_q_full(q), q_uses & 1, 3);
-                ++q_uses;
-                SFA_TRACE(tr, tiles_of(q), q, 4);
-            } else {
-                flush_pv();   // an item this warp sits out: nothing to overlap with, and its ring slot must not be held
-            }
-            for (int j = 0; j < n_q && ok; ++j) {
-                // ---- S(q, j) = Q_q K_j^T
+            const Item it = next_item(k, ok);
+            if (it.index >= p.total_items) break;
+            for (int j = 0; j < it.n_max && ok; ++j) {
                 const uint32_t gi = ring + 2u * (uint32_t)j, kslot = gi % NSTAGE;
-                const uint32_t t = tiles_of(q) + (uint32_t)j;      // running tile count of this query tile
-                int buf = 0;
                 ok = wait_all(bar_kv_full(kslot), (gi / NSTAGE) & 1, 2);
-                SFA_TRACE(tr, t, q, 0);
-                // the buffer's previous scores must have been loaded into registers by their warpgroup
-                if constexpr (NQ == 2 && kSBufs == 1) {
-                    const int ord = qk_ordinal(it, q, j);
-                    if (ord >= 1) {
-                        const int prev = tile_of_ordinal(it, ord - 1);
-                        const int pq = prev >> 16;
-                        ok = ok && wait_all(bar_s_free(pq), (tiles_of(pq) + (uint32_t)(prev & 0xffff)) & 1, 9);
-                    } else if (has_last) {
-                        ok = ok && wait_all(bar_s_free(last_q), last_parity, 9);
+                const uint64_t k_desc = ring_k_desc + (uint64_t)(kslot * (L::kTileBytes >> 4));
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    const int n_q = q == 0 ? it.n0 : it.n1;
+                    if (j >= n_q) continue;
+                    const uint32_t t = (q == 0 ? tiles0 : tiles1) + (uint32_t)j;   // running tile count of this query tile
+                    if (j == 0) {      // the item's Q tile
+                        ok = ok && wait_all(bar_q_full(q), (q == 0 ? q_uses0 : q_uses1) & 1, 3);
+                        if (q == 0) ++q_uses0; else ++q_uses1;
                     }
-                } else if constexpr (NQ == 2) {
-                    buf = q;
-                    if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
-                } else {
-                    buf = t & 1;
-                    if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
+                    SFA_TRACE(tr, t, q, 0);
+                    // the buffer's previous scores must have been loaded into registers by their warpgroup
+                    int buf = 0;
+                    if constexpr (NQ == 2 && kSBufs == 1) {
+                        if (has_prev) ok = ok && wait_all(bar_s_free(prev_q), prev_t & 1, 9);
+                    } else if constexpr (NQ == 2) {
+                        buf = q;
+                        if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
+                    } else {
+                        buf = t & 1;
+                        if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
+                    }
+                    tc_fence_after();
+                    SFA_TRACE(tr, t, q, 1);
+                    if (ok && elect_one()) {
+                        const uint64_t q_desc = q_desc0 + (uint64_t)(q * (L::kTileBytes >> 4));
+                        const uint32_t s_tmem = tmem_base + T::kSOff + buf * kBlockN;
+                        // start-address field is in 16-byte units and never carries out of its 14 bits (smem < 256 KB)
+#pragma unroll
+                        for (int kc = 0; kc < D / 16; ++kc) {
+                            const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
+                            mma_ss(s_tmem, q_desc + off16, k_desc + off16, idesc_qk, kc > 0);
+                        }
+                        tc_commit(bar_s_full(q));
+                        if (j == n_q - 1) tc_commit(bar_q_empty(q));
+                    }
+                    __syncwarp();
+                    SFA_TRACE(tr, t, q, 2);
+                    has_prev = true; prev_q = q; prev_t = t;
                 }
-                tc_fence_after();
-                SFA_TRACE(tr, t, q, 1);
-                if (ok && elect_one()) {
-                    issue_qk(kslot, buf);
-                    tc_commit(bar_s_full(q));
-                    if (j == n_q - 1) tc_commit(bar_q_empty(q));
-                    if constexpr (!SOFTREL)
-                        for (int u = users(it, j); u <= NQ; ++u) tc_commit(bar_kv_empty(kslot));
-                }
+                if (ok && elect_one()) tc_commit(bar_kv_empty(kslot));   // every Q.K that reads K_j has been issued
                 __syncwarp();
-                SFA_TRACE(tr, t, q, 2);
-                // ---- P.V of the previous tile (the previous item's last one when j == 0)
-                flush_pv();
-                pend.valid = true;
-                pend.gi = gi + 1u;
-                pend.t = t;
-                pend.accumulate = j > 0;
-                pend.releases = NQ - users(it, j) + 1;
             }
-            // A parity wait is only sound for a waiter that has seen the phase before: follow the phases of the ring
-            // loads this warp does not consume (key tiles only the other query tile needs), or a later wait on the
-            // same slot could take a stale phase for the one it wants.
-            for (int j = n_q; j < it.n_max && ok; ++j) {
-                const uint32_t gk = ring + 2u * (uint32_t)j, gv = gk + 1u;
-                ok = wait_all(bar_kv_full(gk % NSTAGE), (gk / NSTAGE) & 1, 14);
-                ok = ok && wait_all(bar_kv_full(gv % NSTAGE), (gv / NSTAGE) & 1, 14);
-            }
-            if constexpr (NQ == 2 && kSBufs == 1) {
-                const int total = it.n[0] + it.n[NQ - 1];
-                if (total > 0) {
-                    const int lt = tile_of_ordinal(it, total - 1);
-                    last_q = lt >> 16;
-                    last_parity = (tiles_of(last_q) + (uint32_t)(lt & 0xffff)) & 1;
-                    has_last = true;
-                }
-            }
-            tiles_a += (uint32_t)it.n[0];
-            tiles_b += (uint32_t)it.n[NQ - 1];
+            tiles0 += (uint32_t)it.n0;
+            tiles1 += (uint32_t)it.n1;
             ring += 2u * (uint32_t)it.n_max;
         }
-        flush_pv();
-    } else if (warp < kSoftmaxWarps) {
+    } else if (warp == kWarpPV) {
+        // =============================================================== P.V issuer: O(q) += P(q, j) V_j for both query tiles
+        // (TS: A = P in TMEM, B = V in smem, MN-major), in two halves of 64 keys each, in the order the softmax
+        // warpgroups produce P.  The first P.V of an item overwrites O: its P arrives only after the warpgroup has
+        // read the previous item's O (see the deferred epilogue below).
+        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
+        constexpr uint32_t idesc_pv = mma_idesc(BF16, 0, 1, kBlockM, D);
+        // V: MN-major (head_dim contiguous), 8-key groups 1024 B apart, next 64 head_dim columns one sub-tile further.
+        constexpr uint64_t desc_v = smem_desc_sw128(L::kSubTileBytes, 1024);
+        const uint64_t ring_v_desc = smem_desc_at(desc_v, smem_base + L::kRingOff);
+        bool ok = true;
+        uint32_t ring = 0, tiles0 = 0, tiles1 = 0;
+#ifdef SFA_PROBES
+        const bool tr = trace_cta && lane == 0;
+#endif
+        for (int k = 0; ok; ++k) {
+            const Item it = next_item(k, ok);
+            if (it.index >= p.total_items) break;
+            for (int j = 0; j < it.n_max && ok; ++j) {
+                const uint32_t gi = ring + 2u * (uint32_t)j + 1u, vslot = gi % NSTAGE;
+                ok = wait_all(bar_kv_full(vslot), (gi / NSTAGE) & 1, 4);
+                const uint64_t v_desc = ring_v_desc + (uint64_t)(vslot * (L::kTileBytes >> 4));
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) {
+                    const int n_q = q == 0 ? it.n0 : it.n1;
+                    if (j >= n_q) continue;
+                    const uint32_t t = (q == 0 ? tiles0 : tiles1) + (uint32_t)j;
+                    const uint32_t p_tmem = tmem_base + T::kPOff + q * (kBlockN / 2);
+                    const uint32_t o_tmem = tmem_base + T::kOOff + q * D;
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {      // keys [64 * half, 64 * half + 64)
+                        ok = ok && wait_all(bar_p_ready(q, half), t & 1, 5);
+                        tc_fence_after();
+                        SFA_TRACE(tr, t, q, half == 0 ? 3 : 5);
+                        if (ok && elect_one()) {
+#pragma unroll
+                            for (int kk = 0; kk < kBlockN / 32; ++kk) {
+                                const int kc = half * (kBlockN / 32) + kk;
+                                mma_ts(o_tmem, p_tmem + kc * 8, v_desc + (uint64_t)(kc * (2048 >> 4)), idesc_pv, j > 0 || kc > 0);
+                            }
+                            if (half == 1) tc_commit(bar_pv_done(q));
+                        }
+                        __syncwarp();
+                    }
+                    SFA_TRACE(tr, t, q, 6);
+                }
+                if (ok && elect_one()) tc_commit(bar_kv_empty(vslot));   // every P.V that reads V_j has been issued
+                __syncwarp();
+            }
+            tiles0 += (uint32_t)it.n0;
+            tiles1 += (uint32_t)it.n1;
+            ring += 2u * (uint32_t)it.n_max;
+        }
+    } else {
         // =============================================================== softmax warpgroups
         // Warpgroup q serves query tile q; thread i owns row i of the tile (TMEM lane i).
         if constexpr (kSetRegs) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(R::kSoftmax));
         constexpr int kCols = kBlockN;
         const int q = warp >> 2;
         const int row_in_tile = (warp & 3) * 32 + lane;
-        const bool wg_leader = (warp & 3) == 0 && lane == 0;   // issues the TMA stores, hands ring slots back
+        const bool wg_leader = (warp & 3) == 0 && lane == 0;   // issues the warpgroup's TMA stores
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
         const uint32_t p_tmem = lane_base + T::kPOff + q * (kBlockN / 2);   // my packed P columns
         const uint32_t o_tmem = lane_base + T::kOOff + q * D;
@@ -616,13 +586,51 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         const uint64_t sl2_2 = pack_f2(sl2, sl2);
         bool ok = true;
         uint32_t tiles = 0;         // key tiles this warpgroup has been through in earlier items
-        uint32_t ring = 0;          // K/V tiles of earlier items
 #ifdef SFA_PROBES
         const bool tr = trace_cta && lane == 0 && (warp & 3) == 0;
 #endif
-        auto release = [&](const Item<NQ>& it, uint32_t gi, int j) {   // hand a ring slot back (SOFTREL)
-            if (wg_leader)
-                for (int u = users(it, j); u <= NQ; ++u) mbar_arrive(bar_kv_empty(gi % NSTAGE));
+        // The epilogue of an item is DEFERRED into the next item's first tile: once that tile's P sits in TMEM (its
+        // hand-over to the P.V warp held back), the warpgroup writes the finished item's O - by then the item's
+        // last P.V is long done, so nothing is waited for, and the score buffer of the new item was drained first.
+        // What the deferred epilogue needs of the finished item:
+        bool pending = false;
+        float pend_inv_l = 0.f, pend_lse = 0.f;
+        int pend_h = 0, pend_b = 0, pend_row0 = 0;
+        // O / l -> swizzled staging tile -> TMA store (rows past seqlen_q are clipped by the tensor map), LSE -> global
+        auto write_item = [&](bool have_o, float inv_l, float lse, int h_, int b_, int row0) {
+#pragma unroll 1
+            for (int c = 0; c < kSub; ++c) {
+                uint32_t o[64];
+                if (have_o) {
+                    tmem_ld32(o_tmem + 64 * c, o);
+                    tmem_ld32(o_tmem + 64 * c + 32, o + 32);
+                    tmem_wait_ld();
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 64; ++i) o[i] = 0u;
+                }
+                uint32_t packed[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
+                // the staging tile is free once the previous TMA store has read it
+                if (wg_leader) bulk_wait_read0();
+                named_bar_sync(1 + q, 128);
+                // row r of the tile is 128 B; its 16-byte chunk i sits at chunk i ^ (r & 7) (the 128-byte swizzle
+                // of the tensor map): eight consecutive rows hit eight different bank groups
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    st_shared_v4(stage + row_in_tile * 128 + ((i ^ (row_in_tile & 7)) << 4), packed[4 * i],
+                                 packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+                fence_proxy_async_smem();
+                named_bar_sync(1 + q, 128);
+                if (wg_leader) {
+                    tma_store_4d(&o_map, stage, 64 * c, h_, row0, b_);
+                    bulk_commit();
+                }
+            }
+            const int row = row0 + row_in_tile;
+            if (row < p.seqlen_q && p.lse) p.lse[((int64_t)b_ * p.heads_q + h_) * p.seqlen_q + row] = lse;
         };
         // With a score buffer of their own (head_dim 64) nothing couples the two warpgroups, and started together
         // they stay in lockstep: both in the exp2 loop (MUFU contended), then both in the load + max phase (MUFU
@@ -632,14 +640,26 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             while (clock64() - t0 < p.stagger_cycles) __nanosleep(64);
         }
         for (int k = 0; ok; ++k) {
-            const int item = next_item(k, ok);
-            if (item >= p.total_items) break;
-            Item<NQ> it;
-            decode_item<NQ>(p, item, it);
-            const int n_q = q == 0 ? it.n[0] : it.n[NQ - 1];   // (no runtime-indexed array: it would live in local memory)
-            const int row = it.m0 + q * kBlockM + row_in_tile;
+            const Item it = next_item(k, ok);
+            const bool end = it.index >= p.total_items;
+            const int n_q = end ? 0 : (q == 0 ? it.n0 : it.n1);   // (no runtime-indexed array: it would live in local memory)
+            const int row0 = it.m0 + q * kBlockM;
+            if (n_q == 0) {
+                // nothing to hide the pending epilogue behind: write it now
+                if (pending && ok) {
+                    ok = wait_barrier(bar_pv_done(q), (tiles - 1u) & 1, p.error_flag, 10);
+                    tc_fence_after();
+                    write_item(true, pend_inv_l, pend_lse, pend_h, pend_b, pend_row0);
+                    pending = false;
+                }
+                if (end) break;
+                // rows that see no key at all (causal with more queries than keys): O = 0, LSE = -inf
+                if (row0 < p.seqlen_q) write_item(false, 0.f, -INFINITY, it.h, it.b, row0);
+                continue;
+            }
+            SFA_TRACE(tr, tiles, q, 15);
+            const int row = row0 + row_in_tile;
             const int key_limit = p.causal ? row + causal_shift : INT_MAX;   // last visible key of this row
-            SFA_TRACE(tr && n_q > 0, tiles, q, 15);
             float m_used = -INFINITY;   // reference maximum (raw score units) the exponentials are taken against
             uint64_t l_acc[2] = {0ull, 0ull};   // four partial row sums as two f32x2 accumulators
 
@@ -660,11 +680,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_s_free(free_idx));
-                if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)j, j);   // Q.K(q, j) is done with K_j
                 SFA_TRACE(tr, t, q, 9);
                 const int key0 = j * kBlockN;
-                const bool need_mask = (key0 + kBlockN - 1 > it.m0 + q * kBlockM + causal_shift && p.causal) ||
-                                       (key0 + kBlockN > p.seqlen_k);
+                const bool need_mask = (key0 + kBlockN - 1 > row0 + causal_shift && p.causal) || (key0 + kBlockN > p.seqlen_k);
                 const int lim = min(key_limit, p.seqlen_k - 1) - key0;   // columns <= lim stay (masked tiles only)
                 // ---- row maximum: four independent chains
                 float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -682,14 +700,14 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 scan_half(kCols / 2);
                 const float mx_all = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
 
-                // P(q, j-1) is still being read by the tensor pipe, and O(q) still accumulated into, until pv_done
-                bool pv_waited = j == 0;
+                // P(q) of the previous tile (the previous ITEM's last one when j == 0) is still being read by the
+                // tensor pipe, and O(q) still accumulated into, until pv_done
+                bool pv_waited = t == 0;
                 auto wait_pv = [&]() {
                     if (!pv_waited) {
                         ok = wait_barrier(bar_pv_done(q), (t - 1) & 1, p.error_flag, 8);
                         tc_fence_after();
                         pv_waited = true;
-                        if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)(j - 1) + 1u, j - 1);   // V_{j-1}
                     }
                 };
                 const float m_new = fmaxf(m_used, mx_all);
@@ -717,6 +735,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 }
                 const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
                 const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
+                const bool hold = j == 0 && pending;   // the hand-over of this P waits for the deferred epilogue
                 SFA_TRACE(tr, t, q, 10);
                 // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
                 // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
@@ -754,7 +773,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                             tmem_wait_st();
                             tc_fence_before();
                             __syncwarp();
-                            if (lane == 0) {
+                            if (lane == 0 && !hold) {
                                 if (i == kPairs - 1) mbar_arrive(bar_p_ready(q, kPairs / 32 - 1));
                                 else mbar_arrive(bar_p_ready(q, (i >> 5) - 1));
                             }
@@ -764,70 +783,39 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 };
                 if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
                 else exp_and_store(std::integral_constant<int, 0>{});
+                if (hold) {
+                    // the finished item's last P.V was waited for above (wait_pv at the first P store); O is final
+                    SFA_TRACE(tr, t - 1u, q, 13);
+                    write_item(true, pend_inv_l, pend_lse, pend_h, pend_b, pend_row0);
+                    pending = false;
+                    SFA_TRACE(tr, t - 1u, q, 14);
+                    // O has been read (tcgen05.wait::ld inside): the new item's first P.V may overwrite it
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive(bar_p_ready(q, 0));
+                        mbar_arrive(bar_p_ready(q, 1));
+                    }
+                }
             }
-
-            // ---- end of the item: O / l -> swizzled staging tile -> TMA store, LSE -> global
+            // ---- end of the item: its O is written later (deferred epilogue)
             float l0, l1, l2, l3;
             unpack_f2(l_acc[0], l0, l1);
             unpack_f2(l_acc[1], l2, l3);
             const float l_sum = (l0 + l1) + (l2 + l3);
-            const float inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
-            if (n_q > 0 && ok) {
-                ok = wait_barrier(bar_pv_done(q), (tiles + (uint32_t)n_q - 1u) & 1, p.error_flag, 10);
-                tc_fence_after();
-                if constexpr (SOFTREL) release(it, ring + 2u * (uint32_t)(n_q - 1) + 1u, n_q - 1);
-            }
-            SFA_TRACE(tr && n_q > 0, tiles + (uint32_t)n_q - 1u, q, 13);
-            if (it.m0 + q * kBlockM < p.seqlen_q) {      // uniform over the warpgroup
-#pragma unroll
-                for (int c = 0; c < kSub; ++c) {
-                    uint32_t o[64];
-                    if (n_q > 0) {
-                        tmem_ld32(o_tmem + 64 * c, o);
-                        tmem_ld32(o_tmem + 64 * c + 32, o + 32);
-                        tmem_wait_ld();
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 64; ++i) o[i] = 0u;
-                    }
-                    uint32_t packed[32];
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
-                    // the staging tile is free once the previous TMA store has read it
-                    if (wg_leader) bulk_wait_read0();
-                    named_bar_sync(1 + q, 128);
-                    // row r of the tile is 128 B; its 16-byte chunk i sits at chunk i ^ (r & 7) (the 128-byte swizzle
-                    // of the tensor map): eight consecutive rows hit eight different bank groups
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        st_shared_v4(stage + row_in_tile * 128 + ((i ^ (row_in_tile & 7)) << 4), packed[4 * i],
-                                     packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
-                    fence_proxy_async_smem();
-                    named_bar_sync(1 + q, 128);
-                    if (wg_leader) {
-                        tma_store_4d(&o_map, stage, 64 * c, it.h, it.m0 + q * kBlockM, it.b);   // rows past seqlen_q are clipped
-                        bulk_commit();
-                    }
-                }
-                if (row < p.seqlen_q && p.lse) {
-                    const float lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
-                    p.lse[((int64_t)it.b * p.heads_q + it.h) * p.seqlen_q + row] = lse;
-                }
-            }
-            SFA_TRACE(tr && n_q > 0, tiles + (uint32_t)n_q - 1u, q, 14);
+            pend_inv_l = l_sum > 0.f ? 1.f / l_sum : 0.f;
+            pend_lse = l_sum > 0.f ? (m_used * sl2 + log2f(l_sum)) * kLn2 : -INFINITY;
+            pend_h = it.h; pend_b = it.b; pend_row0 = row0;
+            pending = true;
             tiles += (uint32_t)n_q;
-            ring += 2u * (uint32_t)it.n_max;
         }
         if (wg_leader) bulk_wait_all0();   // the stores read shared memory: it must outlive them
-    } else {
-        if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));   // idle warp of the third warpgroup
     }
 
     // ---- teardown: every tcgen05 operation of this CTA has completed once the softmax warps are here
     tc_fence_before();
     __syncthreads();
-    if (warp == kSoftmaxWarps + 1) {
+    if (warp == kWarpQK) {
         tc_fence_after();
         tmem_dealloc(tmem_base, T::kCols);
     }
@@ -875,10 +863,10 @@ struct FwdMaps {
     alignas(64) CUtensorMap q, k, v, o;
 };
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, bool SOFTREL>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY>
 int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, SOFTREL>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -920,24 +908,24 @@ int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cuda
 template <bool BF16>
 int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, int nq, int sm_count, cudaStream_t stream) {
     const FwdTuning& tune = fwd_tuning();
-#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, SR_) \
-    return launch_instance<D_, NQ_, NS_, BF16, POLY_, SR_>(m, p, batch, sm_count, stream)
+    (void)tune;
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_>(m, p, batch, sm_count, stream)
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, false);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0);
 #ifdef SFA_PROBES
-        if (tune.softrel == 1) SFA_LAUNCH(128, 2, 4, 0, true);
-        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, false);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2);
 #endif
-        SFA_LAUNCH(128, 2, 4, 0, false);
+        SFA_LAUNCH(128, 2, 4, 0);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, false);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0);
 #ifdef SFA_PROBES
-    if (tune.softrel == 1) SFA_LAUNCH(64, 2, 6, 2, true);
-    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, false);
+    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0);
+    if (tune.poly == 3) SFA_LAUNCH(64, 2, 6, 3);
 #endif
     // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
     // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2, false);
+    SFA_LAUNCH(64, 2, 6, 2);
 #undef SFA_LAUNCH
 }
 

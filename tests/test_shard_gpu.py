@@ -79,6 +79,7 @@ def test_publish_and_merge_form_matches_peer_form():
     q, kc, vc = _rand((B, Hq, D), dtype, 4).cuda(), _rand((B, M, Hkv, D), dtype, 5).cuda(), _rand((B, M, Hkv, D), dtype, 6).cuda()
     seqlens = torch.tensor([2000], dtype=torch.int32)
     o_ref, lse_ref = naive.decode_attention(q.cpu(), kc.cpu(), vc.cpu(), seqlens)
+    mag, _ = naive.decode_attention(q.cpu(), kc.cpu(), vc.cpu().abs(), seqlens)
     rows = B * Hq
     gathered = torch.empty((world, rows * (D + 1)), dtype=torch.float32, device="cuda")
     for r in range(world):

@@ -16,11 +16,11 @@ os.environ["SFA_PROBES_LIB"] = "1"
 import starflashattention_b200 as sfa  # noqa: E402
 from starflashattention_b200 import _capi  # noqa: E402
 
-NAMES = {7: "mma: item start", 4: "mma: Q tile acquired", 0: "mma: K tile acquired", 1: "mma: S buffer acquired, QK issue",
-         2: "mma: QK issued + committed", 3: "mma: V tile, P half 0 acquired, PVa issue", 5: "mma: P half 1 acquired, PVb issue",
-         6: "mma: PVb issued + committed",
+NAMES = {0: "qk : K (and Q) tile acquired", 1: "qk : S buffer acquired, QK issue",
+         2: "qk : QK issued + committed", 3: "pv : V tile, P half 0 acquired, PVa issue", 5: "pv : P half 1 acquired, PVb issue",
+         6: "pv : PVb issued + committed",
          15: "wg : item start", 8: "wg : S seen", 9: "wg : S-free arrive", 10: "wg : exp start", 11: "wg : P half 0 arrive",
-         12: "wg : P half 1 arrive", 13: "wg : last P.V of the item seen (epilogue start)", 14: "wg : O stored (TMA store issued), LSE written"}
+         12: "wg : P half 1 arrive", 13: "wg : deferred epilogue of the item starts (inside the next item's first tile)", 14: "wg : O stored (TMA store issued), LSE written"}
 
 
 def main():
