@@ -169,6 +169,15 @@ __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
     }
 }
 
+// conversion pinned in program order like the other members of the exp2 loop
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack_pair_v(float lo, float hi) {
+    uint32_t r;
+    if constexpr (BF16) asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    else asm volatile("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
 // Register split between the softmax warpgroups and the warpgroup holding the producer / issuer warps.
 // setmaxnreg.inc blocks until the CTA's own pool (registers per thread at launch x threads) can cover the
 // request, so the split must fit in that pool exactly - an over-subscribed split hangs the kernel.
@@ -266,7 +275,7 @@ __device__ __forceinline__ Item decode_item(const FwdParams& p, int idx) {
 }
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER>
 __global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const __grid_constant__ CUtensorMap o_map, const FwdParams p) {
@@ -735,7 +744,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 }
                 const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
                 const uint64_t neg_m2 = pack_f2(neg_m, neg_m);
-                const bool hold = j == 0 && pending;   // the hand-over of this P waits for the deferred epilogue
+                const bool hold = DEFER && j == 0 && pending;   // the hand-over of this P waits for the deferred epilogue
                 SFA_TRACE(tr, t, q, 10);
                 // ---- P = exp2(S * scale_log2 - m): MUFU for most pairs, an FMA-pipe polynomial for POLY of every 8
                 // pairs on tiles without masked (-inf) entries; P leaves for TMEM in blocks of 64 keys.
@@ -743,25 +752,24 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     constexpr int kPoly = decltype(poly_tag)::value;
                     constexpr int kPairs = kCols / 2;
                     constexpr int kAhead = 3;            // pairs between the scale FFMA2 and its MUFUs
+                    // pairs between a pair's two MUFUs and the instructions that consume their results (row sum,
+                    // conversion): the warp issues in order, so a consumer right behind its MUFU stalls the MUFUs
+                    // of the following pairs for one MUFU latency per pair (measured: 24 cycles per pair against 16
+                    // of MUFU time, profiles/r1_fwd_tuning.md third pass)
+                    constexpr int kDelay = EXPDELAY;
                     uint64_t xq[kAhead];                 // scaled scores waiting for their exp2
+                    uint64_t done[kDelay > 0 ? kDelay : 1];   // exponentials waiting for their consumers
                     auto scale = [&](int i) {
                         return ffma2_v(pack_f2(__uint_as_float(su[2 * i]), __uint_as_float(su[2 * i + 1])), sl2_2, neg_m2);
                     };
 #pragma unroll
                     for (int i = 0; i < kAhead; ++i) xq[i] = scale(i);
                     uint32_t pk[32];
-#pragma unroll
-                    for (int i = 0; i < kPairs; ++i) {
-                        float x0, x1, p0, p1;
-                        unpack_f2(xq[i % kAhead], x0, x1);
-                        if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
-                        if ((i & 7) >= 8 - kPoly) {
-                            unpack_f2(exp2_poly2(x0, x1), p0, p1);
-                        } else {
-                            p0 = ex2_v(x0); p1 = ex2_v(x1);
-                        }
-                        l_acc[i & 1] = fadd2_v(l_acc[i & 1], pack_f2(p0, p1));
-                        pk[i & 31] = pack_pair<BF16>(p0, p1);
+                    auto consume = [&](int i, uint64_t e) {      // pair i: row sum, conversion, store and hand-off of P
+                        float p0, p1;
+                        unpack_f2(e, p0, p1);
+                        l_acc[i & 1] = fadd2_v(l_acc[i & 1], e);
+                        pk[i & 31] = pack_pair_v<BF16>(p0, p1);
                         if ((i & 31) == 31) {
                             if (i == 31) wait_pv();      // the previous tile's P.V must have drained before P is overwritten
                             tmem_st32(p_tmem + (i >> 5) * 32, pk);
@@ -779,6 +787,29 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                             }
                             SFA_TRACE(tr, t, q, i == kPairs - 1 ? 12 : 11);
                         }
+                    };
+#pragma unroll
+                    for (int i = 0; i < kPairs; ++i) {
+                        float x0, x1, p0, p1;
+                        unpack_f2(xq[i % kAhead], x0, x1);
+                        if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
+                        uint64_t e;
+                        if ((i & 7) >= 8 - kPoly) {
+                            e = exp2_poly2(x0, x1);
+                        } else {
+                            p0 = ex2_v(x0); p1 = ex2_v(x1);
+                            e = pack_f2(p0, p1);
+                        }
+                        if constexpr (kDelay == 0) {
+                            consume(i, e);
+                        } else {
+                            if (i >= kDelay) consume(i - kDelay, done[i % kDelay]);
+                            done[i % kDelay] = e;
+                        }
+                    }
+                    if constexpr (kDelay > 0) {
+#pragma unroll
+                        for (int i = kPairs; i < kPairs + kDelay; ++i) consume(i - kDelay, done[i % kDelay]);
                     }
                 };
                 if (POLY > 0 && !need_mask) exp_and_store(std::integral_constant<int, POLY>{});
@@ -808,6 +839,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             pend_h = it.h; pend_b = it.b; pend_row0 = row0;
             pending = true;
             tiles += (uint32_t)n_q;
+            if constexpr (!DEFER) {     // A/B: the epilogue at the end of its own item
+                if (ok) ok = wait_barrier(bar_pv_done(q), (tiles - 1u) & 1, p.error_flag, 10);
+                tc_fence_after();
+                write_item(true, pend_inv_l, pend_lse, pend_h, pend_b, pend_row0);
+                pending = false;
+            }
         }
         if (wg_leader) bulk_wait_all0();   // the stores read shared memory: it must outlive them
     }
@@ -863,10 +900,10 @@ struct FwdMaps {
     alignas(64) CUtensorMap q, k, v, o;
 };
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER>
 int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, EXPDELAY, DEFER>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -909,23 +946,28 @@ template <bool BF16>
 int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, int nq, int sm_count, cudaStream_t stream) {
     const FwdTuning& tune = fwd_tuning();
     (void)tune;
-#define SFA_LAUNCH(D_, NQ_, NS_, POLY_) \
-    return launch_instance<D_, NQ_, NS_, BF16, POLY_>(m, p, batch, sm_count, stream)
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DELAY_, DEFER_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DELAY_, DEFER_>(m, p, batch, sm_count, stream)
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, true);
 #ifdef SFA_PROBES
-        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, true);
+        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, true);
+        if (tune.delay == 3) SFA_LAUNCH(128, 2, 4, 0, 3, true);
+        if (tune.defer == 0) SFA_LAUNCH(128, 2, 4, 0, 2, false);
 #endif
-        SFA_LAUNCH(128, 2, 4, 0);
+        SFA_LAUNCH(128, 2, 4, 0, 2, true);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 2, true);
 #ifdef SFA_PROBES
-    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0);
-    if (tune.poly == 3) SFA_LAUNCH(64, 2, 6, 3);
+    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 2, true);
+    if (tune.delay == 0) SFA_LAUNCH(64, 2, 6, 2, 0, true);
+    if (tune.delay == 3) SFA_LAUNCH(64, 2, 6, 2, 3, true);
+    if (tune.defer == 0) SFA_LAUNCH(64, 2, 6, 2, 2, false);
 #endif
     // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
     // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2);
+    SFA_LAUNCH(64, 2, 6, 2, 2, true);
 #undef SFA_LAUNCH
 }
 
@@ -942,6 +984,8 @@ const FwdTuning& fwd_tuning() {
         v.nq = geti("SFA_FWD_NQ", 0);
         v.v1 = geti("SFA_FWD_V1", 0);
         v.group = geti("SFA_FWD_GROUP", 0);
+        v.delay = geti("SFA_FWD_DELAY", -1);
+        v.defer = geti("SFA_FWD_DEFER", -1);
         return v;
     }();
     return t;
