@@ -26,8 +26,10 @@ struct Flash_decoder_input
     // KV caches, (batch_size, num_layer, memory_max_len, num_heads, head_dim).
     void *__restrict__ k_cache_table = nullptr;
     void *__restrict__ v_cache_table = nullptr;
-    // cos / sin tables, (memory_max_len, rotary_embedding_dim / 2); both null => angles are
-    // evaluated in fp32 inside the kernel.
+    // cos / sin tables, (memory_max_len, rotary_embedding_dim / 2) PACKED (row stride rotary_embedding_dim / 2, as
+    // this library's compute_rotary_table<T> writes them; the reference kernel strides its rows by
+    // rotary_embedding_dim - a table built for it is not interchangeable); both null => angles are evaluated in fp32
+    // inside the kernel.
     void *__restrict__ rotary_cos_table = nullptr;
     void *__restrict__ rotary_sin_table = nullptr;
 

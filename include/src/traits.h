@@ -1,7 +1,8 @@
 // Compile-time shim kept so that `#include <src/traits.h>` and Traits<half,128,128> still name
 // something (reference: src/traits.h:7-26, a shared-memory size calculator).  Tile shapes and
 // shared-memory budgets of the sm_100a kernels are chosen at run time by the host launcher
-// (starflashattention_b200/csrc/launcher.cu); nothing in the library reads this struct.
+// (launch_fwd in starflashattention_b200/csrc/fwd_sm100.cu, launch_decode in csrc/decode_sm100.cu); nothing in the
+// library reads this struct.
 #pragma once
 
 #include <cuda_runtime.h>

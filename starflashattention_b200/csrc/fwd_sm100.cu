@@ -610,6 +610,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
 #pragma unroll 1
             for (int c = 0; c < kSub; ++c) {
                 uint32_t o[64];
+                SFA_STAMP(tr, 4 * c + 0);
                 if (have_o) {
                     tmem_ld32(o_tmem + 64 * c, o);
                     tmem_ld32(o_tmem + 64 * c + 32, o + 32);
@@ -623,8 +624,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 for (int i = 0; i < 32; ++i)
                     packed[i] = pack_pair<BF16>(__uint_as_float(o[2 * i]) * inv_l, __uint_as_float(o[2 * i + 1]) * inv_l);
                 // the staging tile is free once the previous TMA store has read it
+                SFA_STAMP(tr, 4 * c + 1);
                 if (wg_leader) bulk_wait_read0();
                 named_bar_sync(1 + q, 128);
+                SFA_STAMP(tr, 4 * c + 2);
                 // row r of the tile is 128 B; its 16-byte chunk i sits at chunk i ^ (r & 7) (the 128-byte swizzle
                 // of the tensor map): eight consecutive rows hit eight different bank groups
 #pragma unroll
@@ -637,7 +640,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     tma_store_4d(&o_map, stage, 64 * c, h_, row0, b_);
                     bulk_commit();
                 }
+                SFA_STAMP(tr, 4 * c + 3);
             }
+            SFA_STAMP(tr, 8);
             const int row = row0 + row_in_tile;
             if (row < p.seqlen_q && p.lse) p.lse[((int64_t)b_ * p.heads_q + h_) * p.seqlen_q + row] = lse;
         };
@@ -839,11 +844,15 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
             pend_h = it.h; pend_b = it.b; pend_row0 = row0;
             pending = true;
             tiles += (uint32_t)n_q;
-            if constexpr (!DEFER) {     // A/B: the epilogue at the end of its own item
+            if constexpr (!DEFER) {     // the epilogue at the end of its own item
+                SFA_STAMP(tr, 9);
                 if (ok) ok = wait_barrier(bar_pv_done(q), (tiles - 1u) & 1, p.error_flag, 10);
                 tc_fence_after();
+                SFA_TRACE(tr, tiles - 1u, q, 13);
                 write_item(true, pend_inv_l, pend_lse, pend_h, pend_b, pend_row0);
                 pending = false;
+                SFA_TRACE(tr, tiles - 1u, q, 14);
+                SFA_STAMP(tr, 10);
             }
         }
         if (wg_leader) bulk_wait_all0();   // the stores read shared memory: it must outlive them
@@ -948,26 +957,26 @@ int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, 
     (void)tune;
 #define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DELAY_, DEFER_) \
     return launch_instance<D_, NQ_, NS_, BF16, POLY_, DELAY_, DEFER_>(m, p, batch, sm_count, stream)
+    // DELAY (pairs between a pair's MUFUs and its consumers in the exp2 loop) and DEFER (epilogue inside the next
+    // item's first tile) as measured on C3 / C2 (profiles/r2_fwd_tuning.md): 2 / 0 pairs, not deferred.
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, true);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, false);
 #ifdef SFA_PROBES
-        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, true);
-        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, true);
-        if (tune.delay == 3) SFA_LAUNCH(128, 2, 4, 0, 3, true);
-        if (tune.defer == 0) SFA_LAUNCH(128, 2, 4, 0, 2, false);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, false);
+        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, false);
+        if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true);
 #endif
-        SFA_LAUNCH(128, 2, 4, 0, 2, true);
+        SFA_LAUNCH(128, 2, 4, 0, 2, false);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 2, true);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, false);
 #ifdef SFA_PROBES
-    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 2, true);
-    if (tune.delay == 0) SFA_LAUNCH(64, 2, 6, 2, 0, true);
-    if (tune.delay == 3) SFA_LAUNCH(64, 2, 6, 2, 3, true);
-    if (tune.defer == 0) SFA_LAUNCH(64, 2, 6, 2, 2, false);
+    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0, false);
+    if (tune.delay == 2) SFA_LAUNCH(64, 2, 6, 2, 2, false);
+    if (tune.defer == 1) SFA_LAUNCH(64, 2, 6, 2, 0, true);
 #endif
     // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
     // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2, 2, true);
+    SFA_LAUNCH(64, 2, 6, 2, 0, false);
 #undef SFA_LAUNCH
 }
 

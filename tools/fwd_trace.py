@@ -20,7 +20,7 @@ NAMES = {0: "qk : K (and Q) tile acquired", 1: "qk : S buffer acquired, QK issue
          2: "qk : QK issued + committed", 3: "pv : V tile, P half 0 acquired, PVa issue", 5: "pv : P half 1 acquired, PVb issue",
          6: "pv : PVb issued + committed",
          15: "wg : item start", 8: "wg : S seen", 9: "wg : S-free arrive", 10: "wg : exp start", 11: "wg : P half 0 arrive",
-         12: "wg : P half 1 arrive", 13: "wg : deferred epilogue of the item starts (inside the next item's first tile)", 14: "wg : O stored (TMA store issued), LSE written"}
+         12: "wg : P half 1 arrive", 13: "wg : epilogue of the item starts (last P.V seen)", 14: "wg : O stored (TMA store issued), LSE written"}
 
 
 def main():
@@ -53,6 +53,11 @@ def main():
             print(f"{t - t0:7d}  {name}")
     window(j0, j0 + nj, f"steady state, tiles {j0} .. {j0 + nj - 1}")
     window(61, 67, "item boundary of CTA 0 (first item: 63 / 64 tiles)")
+    e = [buf[i] for i in range(11)]
+    if e[10] and e[9]:
+        print("last epilogue of CTA 0's warp 0 (cycles from its start): P.V seen +%d | half 0: O loaded +%d, staging free +%d, "
+              "written + fenced + store issued +%d | half 1: start +%d, O loaded +%d, staging free +%d, store issued +%d | "
+              "LSE written, done +%d" % (e[0] - e[9], e[1] - e[9], e[2] - e[9], e[3] - e[9], e[4] - e[9], e[5] - e[9], e[6] - e[9], e[7] - e[9], e[10] - e[9]))
     t_in, t_setup, t_out = (buf[i] for i in (24, 25, 28))
     if t_in and t_out:
         print(f"CTA 0: {t_out - t_in} cycles in all; entry -> set-up done {t_setup - t_in}")
