@@ -241,6 +241,9 @@ def timed(fn, steps, dev, world, dist, flush=None):
             # dirty in L2 and their write-back would share HBM with the timed kernel's reads
             wbuf.zero_()
             rbuf.max()
+            # ~0.3 ms of device-side spinning: the host has enqueued the timed call before the GPU gets to e0, so
+            # the interval holds the kernels and not the host's launch path
+            torch.cuda._sleep(600000)
             e0.record(); fn(); e1.record()
             torch.cuda.synchronize()
             ms += e0.elapsed_time(e1)

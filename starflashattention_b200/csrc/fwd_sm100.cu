@@ -80,7 +80,7 @@ __device__ unsigned long long g_fwd_probe[32 + 4096];
 // Bounded mbarrier wait: a mis-programmed pipeline must end the kernel, not hang the GPU.  The bound is a count of
 // failed try_waits (each suspends the thread for a hardware time slice), not a clock: this code is inlined at every
 // wait of the kernel, and the %globaltimer version made up a third of its instructions (instruction cache).
-constexpr uint32_t kMaxWaitSpins = 1u << 24;
+constexpr uint32_t kMaxWaitSpins = 1u << 19;   // measured: 2^24 failed try_waits take about 60 s, so this is about 2 s
 __device__ __forceinline__ bool wait_barrier(uint32_t bar, uint32_t parity, int* error_flag, int code) {
     if (mbar_try_wait(bar, parity)) return true;
     uint32_t spins = 0;
@@ -158,6 +158,19 @@ __device__ __forceinline__ uint64_t exp2_poly2(float x0, float x1) {
     r1 = __int_as_float(__float_as_int(r1) + (__float_as_int(t1) << 23));
     return pack_f2(r0, r1);
 }
+// The same polynomial with scalar arithmetic: the packed FADD2 / FFMA2 issue every second cycle, so they save nothing
+// over two scalar instructions, and the scalar form needs no pack / unpack moves (tools/micro/exp_poly.cu: 14.2 against
+// 14.8 cycles per pair and sub-partition with two warps, a quarter of the pairs on the polynomial; 16.6 without it).
+__device__ __forceinline__ float exp2_poly1(float x) {
+    constexpr float kMagic = 12582912.f;   // 1.5 * 2^23
+    x = fmaxf(x, -125.f);
+    const float t = x + kMagic;
+    const float f = x - (t - kMagic);      // x - round(x)
+    float r = fmaf(0.055171459913253784f, f, 0.2426108568906784f);
+    r = fmaf(r, f, 0.6932609677314758f);
+    r = fmaf(r, f, 0.9999281167984009f);
+    return __int_as_float(__float_as_int(r) + (__float_as_int(t) << 23));
+}
 template <bool BF16>
 __device__ __forceinline__ uint32_t pack_pair(float lo, float hi) {
     if constexpr (BF16) {
@@ -219,9 +232,9 @@ struct FwdSmem {
     // O staging for the TMA store: per query tile one 128-row x 64-column sub-tile (used D / 64 times per item)
     static constexpr int kStageOff = kRingOff + NSTAGE * kTileBytes;
     static constexpr int kBarOff = kStageOff + NQ * kSubTileBytes;
-    // barriers: q_full[NQ], q_empty[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], s_full[NQ], p_ready[NQ][2], pv_done[NQ],
-    //           s_free[2], sched_full[2], sched_empty[2]
-    static constexpr int kNumBars = 6 * NQ + 2 * NSTAGE + 6;
+    // barriers: q_full[NQ], q_empty[NQ], kv_full[NSTAGE], kv_empty[NSTAGE], p_ready[NQ][2], pv_done[NQ],
+    //           s_free[2], sched_full[2], sched_empty[2], s_full[2]
+    static constexpr int kNumBars = 5 * NQ + 2 * NSTAGE + 8;
     static constexpr int kSchedOff = (kBarOff + kNumBars * 8 + 15) / 16 * 16;   // two published work items, 32 B each
     static constexpr int kTmemPtrOff = kSchedOff + 64;
     static constexpr int kBytes = kTmemPtrOff + 16;
@@ -275,7 +288,7 @@ __device__ __forceinline__ Item decode_item(const FwdParams& p, int idx) {
 }
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, bool POLYSCALAR>
 __global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const __grid_constant__ CUtensorMap o_map, const FwdParams p) {
@@ -298,15 +311,20 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     auto bar_q_empty = [&](int q) { return bar_base + 8u * (NQ + q); };
     auto bar_kv_full = [&](uint32_t s) { return bar_base + 8u * (2 * NQ + s); };
     auto bar_kv_empty = [&](uint32_t s) { return bar_base + 8u * (2 * NQ + NSTAGE + s); };
-    auto bar_s_full = [&](int q) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + q); };
     // P is handed to the P.V warp in two halves of 64 keys, so P.V of the first half runs under the second's exp2
-    auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (3 * NQ + 2 * NSTAGE + 2 * q + half); };
+    auto bar_p_ready = [&](int q, int half) { return bar_base + 8u * (2 * NQ + 2 * NSTAGE + 2 * q + half); };
     // every P.V of query tile q has completed: P(q) may be overwritten, O(q) may be rescaled / read
-    auto bar_pv_done = [&](int q) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + q); };
+    auto bar_pv_done = [&](int q) { return bar_base + 8u * (4 * NQ + 2 * NSTAGE + q); };
     // warpgroup q has loaded its scores into registers: the next Q.K may overwrite that buffer
-    auto bar_s_free = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + i); };
-    auto bar_sched_full = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 2 + i); };
-    auto bar_sched_empty = [&](int i) { return bar_base + 8u * (6 * NQ + 2 * NSTAGE + 4 + i); };
+    auto bar_s_free = [&](int i) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + i); };
+    auto bar_sched_full = [&](int i) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + 2 + i); };
+    auto bar_sched_empty = [&](int i) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + 4 + i); };
+    // Scores of a tile are in TMEM.  One barrier per query tile (two tiles), or per score buffer (one tile, two
+    // alternating buffers): with ONE barrier for two buffers the Q.K of tiles t and t + 1 can both complete before the
+    // warpgroup looks for tile t, and a parity wait cannot tell "two phases on" from "not yet" - it would hang.
+    auto bar_s_full = [&](int i) { return bar_base + 8u * (5 * NQ + 2 * NSTAGE + 6 + i); };
+    auto s_full_index = [&](int q, uint32_t t) { return NQ == 2 ? q : (int)(t & 1); };
+    auto s_full_parity = [&](uint32_t t) { return NQ == 2 ? (t & 1) : ((t >> 1) & 1); };
     volatile int4* sched_slot = reinterpret_cast<volatile int4*>(smem_gen + L::kSchedOff);   // [2 * entry], [2 * entry + 1]
     volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtrOff);
 
@@ -326,7 +344,6 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         for (int q = 0; q < NQ; ++q) {
             mbar_init(bar_q_full(q), 1);
             mbar_init(bar_q_empty(q), 1);
-            mbar_init(bar_s_full(q), 1);
             mbar_init(bar_p_ready(q, 0), 4);   // one elected arrival per softmax warp of the tile's warpgroup
             mbar_init(bar_p_ready(q, 1), 4);
             mbar_init(bar_pv_done(q), 1);
@@ -334,6 +351,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar_s_free(i), 4);
+            mbar_init(bar_s_full(i), 1);
             mbar_init(bar_sched_full(i), 1);
             mbar_init(bar_sched_empty(i), kSchedConsumers);
         }
@@ -368,6 +386,20 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
     };
     auto wait_all = [&](uint32_t bar, uint32_t parity, int code) {
         return __all_sync(0xffffffffu, wait_barrier(bar, parity, p.error_flag, code)) != 0;
+    };
+    // the same wait as a spin on test_wait: no suspension, so no wake-up latency - for the one wait that sits on the
+    // kernel's critical cycle (POLL bit 0: the Q.K warp on the score buffer; bit 1: the P.V warp on P)
+    auto poll_all = [&](uint32_t bar, uint32_t parity, int code) {
+        uint32_t spins = 0;
+        bool ok_ = true;
+        while (!mbar_test_wait(bar, parity)) {
+            if (++spins >= (1u << 27)) {
+                atomicCAS(p.error_flag, 0, code);
+                ok_ = false;
+                break;
+            }
+        }
+        return __all_sync(0xffffffffu, ok_) != 0;
     };
 
     // Four single-purpose warps beside the softmax warpgroups; with two query tiles they form a third warpgroup so the
@@ -493,10 +525,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     // the buffer's previous scores must have been loaded into registers by their warpgroup
                     int buf = 0;
                     if constexpr (NQ == 2 && kSBufs == 1) {
-                        if (has_prev) ok = ok && wait_all(bar_s_free(prev_q), prev_t & 1, 9);
+                        if (has_prev) ok = ok && ((POLL & 1) ? poll_all(bar_s_free(prev_q), prev_t & 1, 9) : wait_all(bar_s_free(prev_q), prev_t & 1, 9));
                     } else if constexpr (NQ == 2) {
                         buf = q;
-                        if (t >= 1) ok = ok && wait_all(bar_s_free(q), (t - 1) & 1, 9);
+                        if (t >= 1) ok = ok && ((POLL & 1) ? poll_all(bar_s_free(q), (t - 1) & 1, 9) : wait_all(bar_s_free(q), (t - 1) & 1, 9));
                     } else {
                         buf = t & 1;
                         if (t >= 2) ok = ok && wait_all(bar_s_free(t & 1), ((t >> 1) - 1) & 1, 9);
@@ -512,7 +544,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                             const uint32_t off16 = ((kc >> 2) * L::kSubTileBytes + (kc & 3) * 32) >> 4;
                             mma_ss(s_tmem, q_desc + off16, k_desc + off16, idesc_qk, kc > 0);
                         }
-                        tc_commit(bar_s_full(q));
+                        tc_commit(bar_s_full(s_full_index(q, t)));
                         if (j == n_q - 1) tc_commit(bar_q_empty(q));
                     }
                     __syncwarp();
@@ -557,7 +589,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     const uint32_t o_tmem = tmem_base + T::kOOff + q * D;
 #pragma unroll
                     for (int half = 0; half < 2; ++half) {      // keys [64 * half, 64 * half + 64)
-                        ok = ok && wait_all(bar_p_ready(q, half), t & 1, 5);
+                        ok = ok && ((POLL & 2) ? poll_all(bar_p_ready(q, half), t & 1, 5) : wait_all(bar_p_ready(q, half), t & 1, 5));
                         tc_fence_after();
                         SFA_TRACE(tr, t, q, half == 0 ? 3 : 5);
                         if (ok && elect_one()) {
@@ -682,7 +714,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 const int buf = kSBufs == 1 ? 0 : (NQ == 2 ? q : (int)(t & 1));
                 const int free_idx = NQ == 2 ? q : (int)(t & 1);
                 const uint32_t s_tmem = lane_base + T::kSOff + buf * kBlockN;
-                ok = wait_barrier(bar_s_full(q), t & 1, p.error_flag, 7);
+                ok = wait_barrier(bar_s_full(s_full_index(q, t)), s_full_parity(t), p.error_flag, 7);
                 tc_fence_after();
                 SFA_TRACE(tr, t, q, 8);
                 uint32_t su[kCols];
@@ -800,7 +832,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                         if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
                         uint64_t e;
                         if ((i & 7) >= 8 - kPoly) {
-                            e = exp2_poly2(x0, x1);
+                            if constexpr (POLYSCALAR) e = pack_f2(exp2_poly1(x0), exp2_poly1(x1));
+                            else e = exp2_poly2(x0, x1);
                         } else {
                             p0 = ex2_v(x0); p1 = ex2_v(x1);
                             e = pack_f2(p0, p1);
@@ -909,10 +942,10 @@ struct FwdMaps {
     alignas(64) CUtensorMap q, k, v, o;
 };
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, bool POLYSCALAR>
 int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
-    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, EXPDELAY, DEFER>;
+    auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, EXPDELAY, DEFER, POLL, POLYSCALAR>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
@@ -922,10 +955,11 @@ int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cuda
     // Work-item order.  Items that run at the same time should share K/V in L2, and the heavy query blocks of
     // the causal mask should go first (longest processing time first keeps the tail of the schedule short).  So:
     // (batch, head) pairs in groups; inside a group, query blocks from the last to the first, heads innermost.  A
-    // group holds about two grids' worth of items: with 148 CTAs its K/V (~ 39 MB at head_dim 128) stays in L2.
+    // group holds at most one grid's worth of items (C3: 4 heads = 128 items, 16 MB of K/V): with groups of 8 heads
+    // the ncu capture showed 2.71 GB of DRAM reads against 1.61 GB of Q + K + V (profiles/r2_fwd_tuning.md).
     p.m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     p.heads_total = batch * p.heads_q;
-    p.group_heads = (2 * sm_count + p.m_blocks - 1) / p.m_blocks;
+    p.group_heads = sm_count / p.m_blocks;
     // ... but never more than 32 MB of K/V per group (one head's K/V: seqlen_k rows of D elements, twice): at
     // N = 65536, d = 128 that is one head at a time, as many CTAs as there are SMs on the same 32 MB
     const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;
@@ -955,28 +989,30 @@ template <bool BF16>
 int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, int nq, int sm_count, cudaStream_t stream) {
     const FwdTuning& tune = fwd_tuning();
     (void)tune;
-#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DELAY_, DEFER_) \
-    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DELAY_, DEFER_>(m, p, batch, sm_count, stream)
+#define SFA_LAUNCH(D_, NQ_, NS_, POLY_, DELAY_, DEFER_, POLL_, PS_) \
+    return launch_instance<D_, NQ_, NS_, BF16, POLY_, DELAY_, DEFER_, POLL_, PS_>(m, p, batch, sm_count, stream)
     // DELAY (pairs between a pair's MUFUs and its consumers in the exp2 loop) and DEFER (epilogue inside the next
     // item's first tile) as measured on C3 / C2 (profiles/r2_fwd_tuning.md): 2 / 0 pairs, not deferred.
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, false);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, false, 0, false);
 #ifdef SFA_PROBES
-        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, false);
-        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, false);
-        if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, false);
+        if (tune.poly == 12) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, true);
+        if (tune.poly == 11) SFA_LAUNCH(128, 2, 4, 1, 2, false, 0, true);
+        if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true, 0, false);
 #endif
-        SFA_LAUNCH(128, 2, 4, 0, 2, false);
+        SFA_LAUNCH(128, 2, 4, 0, 2, false, 0, false);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, false);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, false, 0, false);
 #ifdef SFA_PROBES
-    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0, false);
-    if (tune.delay == 2) SFA_LAUNCH(64, 2, 6, 2, 2, false);
-    if (tune.defer == 1) SFA_LAUNCH(64, 2, 6, 2, 0, true);
+    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0, false, 0, false);
+    if (tune.poly == 12) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, true);
+    if (tune.poly == 13) SFA_LAUNCH(64, 2, 6, 3, 0, false, 0, true);
+    if (tune.defer == 1) SFA_LAUNCH(64, 2, 6, 2, 0, true, 0, false);
 #endif
     // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
     // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2, 0, false);
+    SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, false);
 #undef SFA_LAUNCH
 }
 
@@ -995,6 +1031,7 @@ const FwdTuning& fwd_tuning() {
         v.group = geti("SFA_FWD_GROUP", 0);
         v.delay = geti("SFA_FWD_DELAY", -1);
         v.defer = geti("SFA_FWD_DEFER", -1);
+        v.poll = geti("SFA_FWD_POLL", 0);
         return v;
     }();
     return t;
