@@ -21,7 +21,8 @@ def rnd(shape, dtype, seed):
 
 def case_fwd():
     for (B, Sq, Sk, H, Hkv, D, causal, dt) in [(1, 256, 256, 2, 2, 128, True, torch.bfloat16), (1, 200, 333, 2, 1, 128, False, torch.float16),
-                                               (2, 640, 640, 2, 2, 128, True, torch.bfloat16), (1, 300, 300, 2, 2, 64, True, torch.float16)]:
+                                               (2, 640, 640, 2, 2, 128, True, torch.bfloat16), (1, 300, 300, 2, 2, 64, True, torch.float16),
+                                               (1, 100, 419, 2, 2, 128, True, torch.float16), (40, 700, 700, 4, 2, 128, True, torch.bfloat16)]:
         q, k, v = rnd((B, Sq, H, D), dt, 1), rnd((B, Sk, Hkv, D), dt, 2), rnd((B, Sk, Hkv, D), dt, 3)
         o, lse = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=causal)
         torch.cuda.synchronize()
