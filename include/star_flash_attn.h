@@ -239,7 +239,7 @@ int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream);
  * Every pointer of `t` is a host pointer; strides are in elements and describe the HOST tensors (a caller may pass a
  * slice of the heads of a larger tensor: head stride must equal head_dim, batch / row strides are free); lse is
  * (batch, heads_q, seqlen_q) resp. (batch, heads_q) fp32 contiguous or NULL.  pieces <= 0: library's choice
- * (about 16 for prefill: (batch entry, block of query rows); 8 for decode: batch ranges).  Device staging is
+ * (about 32 for prefill: (batch entry, block of query rows); 8 for decode: batch ranges).  Device staging is
  * owned by the library (grow-only, per device; released by sfa_release_workspaces).  Not graph-capturable. */
 typedef struct sfa_fwd_host_args {
     sfa_fwd_args t;

@@ -952,19 +952,20 @@ int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cuda
         attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kAlloc);
     });
     SFA_CUDA_CHECK(attr_err);
-    // Work-item order.  Items that run at the same time should share K/V in L2, and the heavy query blocks of
-    // the causal mask should go first (longest processing time first keeps the tail of the schedule short).  So:
-    // (batch, head) pairs in groups; inside a group, query blocks from the last to the first, heads innermost.  A
-    // group holds at most one grid's worth of items (C3: 4 heads = 128 items, 16 MB of K/V): with groups of 8 heads
-    // the ncu capture showed 2.71 GB of DRAM reads against 1.61 GB of Q + K + V (profiles/r2_fwd_tuning.md).
+    // Work-item order.  The heavy query blocks of the causal mask go first (longest processing time first keeps the
+    // tail of the schedule short), and the more (batch, head) pairs one descending sweep over the query blocks covers,
+    // the better the balance: items handed out at the same time then have the same length.  What limits a group is
+    // L2: the K/V of its heads should fit (126 MB).  So: groups of as many heads as 128 MiB of K/V allow; inside a
+    // group, query blocks from the last to the first, heads innermost.  Measured (profiles/r2_fwd_tuning.md, group
+    // sweep): C5 (33.5 MB per head) 1 / 4 / 32 heads 28.98 / 28.22 / 30.46 ms; C3 (4.2 MB per head) 4 / 16 / 64 heads
+    // 3.470 / 3.451 / 3.615 ms; one rank's eighth of C3 4 / 32 heads 0.510 / 0.430 ms.
     p.m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     p.heads_total = batch * p.heads_q;
-    p.group_heads = sm_count / p.m_blocks;
-    // ... but never more than 32 MB of K/V per group (one head's K/V: seqlen_k rows of D elements, twice): at
-    // N = 65536, d = 128 that is one head at a time, as many CTAs as there are SMs on the same 32 MB
-    const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;
-    const long long l2_heads = (32ll << 20) / kv_bytes_per_head;
-    if (p.group_heads > l2_heads) p.group_heads = (int)l2_heads;
+    const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;   // K and V, per query head
+    const long long l2_heads = (128ll << 20) / kv_bytes_per_head;
+    p.group_heads = (int)(l2_heads < p.heads_total ? l2_heads : p.heads_total);
+    // without the causal mask every item has the same length: nothing to balance, so only as many heads as fill the grid
+    if (!p.causal) p.group_heads = (sm_count + p.m_blocks - 1) / p.m_blocks;
 #ifdef SFA_PROBES
     if (fwd_tuning().group > 0) p.group_heads = fwd_tuning().group;
 #endif
@@ -1000,6 +1001,8 @@ int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, 
         if (tune.poly == 12) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, true);
         if (tune.poly == 11) SFA_LAUNCH(128, 2, 4, 1, 2, false, 0, true);
         if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true, 0, false);
+        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, false, 0, false);
+        if (tune.poll == 1) SFA_LAUNCH(128, 2, 4, 0, 2, false, 1, false);
 #endif
         SFA_LAUNCH(128, 2, 4, 0, 2, false, 0, false);
     }

@@ -16,6 +16,8 @@ import starflashattention_b200 as sfa  # noqa: E402
 CFG = {"c3": (torch.bfloat16, 8, 32, 8192, 128, True), "c2": (torch.float16, 4, 16, 4096, 64, False),
        "c5": (torch.bfloat16, 1, 32, 65536, 128, True), "c3nc": (torch.bfloat16, 8, 32, 8192, 128, False),
        "c2b": (torch.float16, 16, 16, 4096, 64, False),
+       # one rank's share of C3 / C5 on 8 GPUs
+       "c3r8": (torch.bfloat16, 1, 32, 8192, 128, True), "c5r8": (torch.bfloat16, 1, 4, 65536, 128, True),
        # head_dim 64 shapes for the warpgroup-stagger sweep
        "d64c": (torch.bfloat16, 4, 16, 4096, 64, True), "d64s": (torch.float16, 16, 16, 1024, 64, False),
        "d64l": (torch.bfloat16, 1, 16, 16384, 64, True)}
