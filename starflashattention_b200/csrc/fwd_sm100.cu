@@ -60,9 +60,9 @@ struct FwdParams {
     int causal;
     float scale_log2;
     int stagger_cycles;   // head start of warpgroup 0 over warpgroup 1 (see launch_fwd)
-    // work-item order: groups of `group_heads` (batch, head) pairs; inside a group query blocks from the last
-    // (heaviest under the causal mask) to the first, heads innermost
-    int m_blocks, heads_total, group_heads, total_items;
+    // work-item order: groups of `group_heads` (batch, head) pairs - the last `tail_heads` heads form one group of
+    // their own; inside a group query blocks from the last (heaviest under the causal mask) to the first, heads innermost
+    int m_blocks, heads_total, group_heads, tail_heads, total_items;
 };
 
 __device__ int g_fwd_error;   // set when an mbarrier wait times out (pipeline bug guard)
@@ -255,11 +255,20 @@ template <int NQ>
 __device__ __forceinline__ Item decode_item(const FwdParams& p, int idx) {
     Item it;
     it.index = idx;
-    const int per_group = p.group_heads * p.m_blocks;
-    const int g = idx / per_group;
-    const int r = idx - g * per_group;
-    const int head0 = g * p.group_heads;
-    const int gh = min(p.group_heads, p.heads_total - head0);
+    const int bulk_heads = p.heads_total - p.tail_heads;
+    const int bulk_items = bulk_heads * p.m_blocks;
+    int head0, gh, r;
+    if (idx < bulk_items) {
+        const int per_group = p.group_heads * p.m_blocks;
+        const int g = idx / per_group;
+        r = idx - g * per_group;
+        head0 = g * p.group_heads;
+        gh = min(p.group_heads, bulk_heads - head0);
+    } else {
+        r = idx - bulk_items;
+        head0 = bulk_heads;
+        gh = p.tail_heads;
+    }
     const int m_desc = r / gh;
     const int head = head0 + (r - m_desc * gh);
     const int m_block = p.m_blocks - 1 - m_desc;
@@ -411,6 +420,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         // a warp of its own, so a Q load never queues behind the K/V ring's waits.
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         int item = blockIdx.x;
+        const uint64_t pol_q = l2_policy_evict_first();   // a Q tile is read once
         int q_loads0 = 0, q_loads1 = 0;   // Q tiles loaded so far, per query tile
         bool ok = true;
         for (int k = 0; ok; ++k) {
@@ -442,8 +452,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     mbar_arrive_expect_tx(bar_q_full(q), L::kTileBytes);
 #pragma unroll
                     for (int s = 0; s < kSub; ++s)
-                        tma_load_4d(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
-                                    64 * s, it.h, it.m0 + q * kBlockM, it.b);
+                        tma_load_4d_hint(smem_base + L::kQOff + q * L::kTileBytes + s * L::kSubTileBytes, &q_map, bar_q_full(q),
+                                         64 * s, it.h, it.m0 + q * kBlockM, it.b, pol_q);
                 }
                 __syncwarp();
                 if (q == 0) ++q_loads0; else ++q_loads1;
@@ -462,6 +472,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         // the odd ones): the next item's first tiles arrive under the current item's last P.V and epilogue.
         if constexpr (kSetRegs) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R::kOther));
         uint32_t ring = 0;          // K/V tiles loaded so far (all items)
+        const uint64_t pol_kv = l2_policy_evict_last();   // every CTA working on the head reads these tiles again
         bool ok = true;
         for (int k = 0; ok; ++k) {
             const Item it = next_item(k, ok);
@@ -474,8 +485,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                     const CUtensorMap* map = (i & 1) ? &v_map : &k_map;
 #pragma unroll
                     for (int s = 0; s < kSub; ++s)
-                        tma_load_4d(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
-                                    bar_kv_full(slot), 64 * s, it.hk, (i >> 1) * kBlockN, it.b);
+                        tma_load_4d_hint(smem_base + L::kRingOff + slot * L::kTileBytes + s * L::kSubTileBytes, map,
+                                         bar_kv_full(slot), 64 * s, it.hk, (i >> 1) * kBlockN, it.b, pol_kv);
                 }
                 __syncwarp();
             }
@@ -623,6 +634,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
         const uint32_t p_tmem = lane_base + T::kPOff + q * (kBlockN / 2);   // my packed P columns
         const uint32_t o_tmem = lane_base + T::kOOff + q * D;
         const uint32_t stage = smem_base + L::kStageOff + q * L::kSubTileBytes;
+        const uint64_t pol_o = l2_policy_evict_first();   // O is written once and not read again
         const float sl2 = p.scale_log2;
         const uint64_t sl2_2 = pack_f2(sl2, sl2);
         bool ok = true;
@@ -669,7 +681,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                 fence_proxy_async_smem();
                 named_bar_sync(1 + q, 128);
                 if (wg_leader) {
-                    tma_store_4d(&o_map, stage, 64 * c, h_, row0, b_);
+                    tma_store_4d_hint(&o_map, stage, 64 * c, h_, row0, b_, pol_o);
                     bulk_commit();
                 }
                 SFA_STAMP(tr, 4 * c + 3);
@@ -952,26 +964,41 @@ int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cuda
         attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kAlloc);
     });
     SFA_CUDA_CHECK(attr_err);
-    // Work-item order.  The heavy query blocks of the causal mask go first (longest processing time first keeps the
-    // tail of the schedule short), and the more (batch, head) pairs one descending sweep over the query blocks covers,
-    // the better the balance: items handed out at the same time then have the same length.  What limits a group is
-    // L2: the K/V of its heads should fit (126 MB).  So: groups of as many heads as 128 MiB of K/V allow; inside a
-    // group, query blocks from the last to the first, heads innermost.  Measured (profiles/r2_fwd_tuning.md, group
-    // sweep): C5 (33.5 MB per head) 1 / 4 / 32 heads 28.98 / 28.22 / 30.46 ms; C3 (4.2 MB per head) 4 / 16 / 64 heads
-    // 3.470 / 3.451 / 3.615 ms; one rank's eighth of C3 4 / 32 heads 0.510 / 0.430 ms.
+    // Work-item order (items are handed out in this order by the atomic counter).  Two forces: (1) items that run at
+    // the same time should share K/V in L2 - few heads at a time, as a grid launched head by head would do; with 8 / 32
+    // heads of C3 interleaved the ncu capture shows 2.7 / 4.3 GB of DRAM reads against 1.61 GB of Q + K + V
+    // (profiles/r2_fwd_tuning.md); (2) under the causal mask the END of the schedule should be a long descending
+    // sweep over many heads, so that the last items handed out are short: the spread of the CTAs' finishing times is
+    // about the length of the items among the last grid's worth (one rank's eighth of C3: 4 / 32 heads per sweep
+    // 0.510 / 0.430 ms; its share of C5: 1 / 4 heads 3.63 / 3.14 ms).  So: the bulk in groups of one grid's worth of
+    // items (query blocks from the last, heaviest, to the first; heads innermost), and the last `tail_heads` heads as ONE
+    // group, sized so that its last grid's worth of items is under 2 % of a CTA's total work, within 128 MiB of K/V.
     p.m_blocks = (p.seqlen_q + NQ * kBlockM - 1) / (NQ * kBlockM);
     p.heads_total = batch * p.heads_q;
-    const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;   // K and V, per query head
-    const long long l2_heads = (128ll << 20) / kv_bytes_per_head;
-    p.group_heads = (int)(l2_heads < p.heads_total ? l2_heads : p.heads_total);
-    // without the causal mask every item has the same length: nothing to balance, so only as many heads as fill the grid
-    if (!p.causal) p.group_heads = (sm_count + p.m_blocks - 1) / p.m_blocks;
+    p.group_heads = (sm_count + p.m_blocks - 1) / p.m_blocks;
+    p.tail_heads = 0;
+    if (p.causal) {
+        const long long kv_bytes_per_head = 4ll * (p.seqlen_k > 0 ? p.seqlen_k : 1) * D / p.group;   // K and V, per query head
+        const long long l2_heads = (128ll << 20) / kv_bytes_per_head;
+        // long sequences (more query blocks than SMs): still four heads per sweep (C5: 1 / 2 / 4 / 8 heads 28.98 / 28.53 /
+        // 28.22 / 28.46 ms)
+        const int few = (int)(l2_heads < 4 ? l2_heads : 4);
+        if (p.group_heads < few) p.group_heads = few;
+        const double per_cta = (double)p.heads_total * p.m_blocks * (p.m_blocks + 1) / sm_count;   // key-tile pairs per CTA
+        long long want = (long long)(2.0 * sm_count / (0.02 * per_cta)) + 1;
+        if (want > l2_heads) want = l2_heads;
+        if (want < p.group_heads) want = p.group_heads;
+        if (want > p.heads_total) want = p.heads_total;
+        p.tail_heads = (int)want;
+    }
 #ifdef SFA_PROBES
-    if (fwd_tuning().group > 0) p.group_heads = fwd_tuning().group;
+    if (fwd_tuning().group > 0) { p.group_heads = fwd_tuning().group; p.tail_heads = 0; }
+    if (fwd_tuning().tail >= 0) p.tail_heads = fwd_tuning().tail < p.heads_total ? fwd_tuning().tail : p.heads_total;
 #endif
     if (p.group_heads < 1) p.group_heads = 1;
     // keep the query heads of one kv head in one group (GQA)
     p.group_heads = (p.group_heads + p.group - 1) / p.group * p.group;
+    p.tail_heads = p.tail_heads / p.group * p.group;
     const long long total = (long long)p.m_blocks * p.heads_total;
     if (total > INT_MAX / 2) return fail(SFA_ERR_UNSUPPORTED, "fwd: more than 2^30 work items");
     p.total_items = (int)total;
@@ -1035,6 +1062,7 @@ const FwdTuning& fwd_tuning() {
         v.delay = geti("SFA_FWD_DELAY", -1);
         v.defer = geti("SFA_FWD_DEFER", -1);
         v.poll = geti("SFA_FWD_POLL", 0);
+        v.tail = geti("SFA_FWD_TAIL", -1);
         return v;
     }();
     return t;

@@ -111,23 +111,48 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     Pipeline& P = *pp;
     if ((rc = pipeline_init(P))) return rc;
 
-    // ---- plan: pieces = (batch entry, block of query rows)
-    // 32 pieces: under the causal mask the last piece is the heaviest and nothing hides its kernel and download;
-    // with 32 it holds 6 % of an entry's work (C5 on 2 GPUs: 20.7 ms with 16 pieces against a 17.9 ms copy floor)
-    if (want_pieces <= 0) want_pieces = 32;
-    int n_r = (want_pieces + B - 1) / B;
+    // ---- plan: pieces = (batch entry, group of kv-heads, block of query rows)
+    // With many batch entries a piece is a block of rows of ALL heads (contiguous on the host).  With few entries
+    // (one long sequence) the heads are cut into groups first: under the causal mask the work of a block of rows
+    // grows with its position while its upload does not, so row blocks alone leave the heavy last blocks' kernels
+    // behind the end of the upload (C5, one sequence: 38.9 ms against a 30.1 ms copy floor); head groups are
+    // independent and uniform.  A group keeps at least 1 KB per row and tensor (pitched DMAs slow down below that).
+    const size_t es = 2;
+    const double in_bytes = es * ((double)B * Sq * Hq * D + 2.0 * B * Sk * Hkv * D);
+    const bool explicit_pieces = want_pieces > 0;
+    if (want_pieces <= 0) {
+        // 32 pieces: the last piece's kernel and download are exposed; pieces of at least 8 MB keep the DMAs efficient
+        want_pieces = 32;
+        const int by_size = (int)(in_bytes / (8 << 20));
+        if (want_pieces > by_size) want_pieces = by_size > B ? by_size : B;
+    }
+    const int hg_min = (int)(1024 / (D * es)) > 0 ? (int)(1024 / (D * es)) : 1;
+    int n_hg = 1;
+    if (B < 4) {
+        n_hg = Hkv / hg_min;
+        if (n_hg > want_pieces / B) n_hg = want_pieces / B;
+        if (n_hg < 1) n_hg = 1;
+    }
+    const int hg = (Hkv + n_hg - 1) / n_hg;               // kv-heads per group
+    n_hg = (Hkv + hg - 1) / hg;
+    const int grp = Hq / Hkv;
+    // head groups of a long sequence are big, uniform pieces (C5: 4 heads x 65536 rows, a 3.3 ms kernel that keeps the
+    // GPU as busy as the full problem does); cutting them into row blocks as well only makes the kernels small and
+    // uneven, and here the kernel time is as long as the copy time
+    const int target = (n_hg > 1 && !explicit_pieces) ? 8 : want_pieces;
+    int n_r = (target + B * n_hg - 1) / (B * n_hg);
     int rows_per = (Sq + n_r - 1) / n_r;
     rows_per = (rows_per + 255) / 256 * 256;              // whole 256-row blocks of the kernel
     n_r = (Sq + rows_per - 1) / rows_per;
     const int shift = Sk - Sq;
-    const size_t es = 2;
-    const size_t q_row = (size_t)Hq * D * es, kv_row = (size_t)Hkv * D * es;
-    if ((rc = ensure(P, kQ0, rows_per * q_row)) || (rc = ensure(P, kQ1, rows_per * q_row)) ||
-        (rc = ensure(P, kO0, rows_per * q_row)) || (rc = ensure(P, kO1, rows_per * q_row)) ||
-        (rc = ensure(P, kKV0, 2 * (size_t)Sk * kv_row + 256)) || (rc = ensure(P, kL0, (size_t)Hq * rows_per * 4)) ||
-        (rc = ensure(P, kL1, (size_t)Hq * rows_per * 4)))
+    const size_t q_row_max = (size_t)hg * grp * D * es, kv_row_max = (size_t)hg * D * es;
+    const size_t kv_half = ((size_t)Sk * kv_row_max + 255) / 256 * 256;
+    if ((rc = ensure(P, kQ0, rows_per * q_row_max)) || (rc = ensure(P, kQ1, rows_per * q_row_max)) ||
+        (rc = ensure(P, kO0, rows_per * q_row_max)) || (rc = ensure(P, kO1, rows_per * q_row_max)) ||
+        (rc = ensure(P, kKV0, 2 * kv_half + 256)) || (rc = ensure(P, kL0, (size_t)hg * grp * rows_per * 4)) ||
+        (rc = ensure(P, kL1, (size_t)hg * grp * rows_per * 4)))
         return rc;
-    if (B > 1 && (rc = ensure(P, kKV1, 2 * (size_t)Sk * kv_row + 256))) return rc;
+    if (B * n_hg > 1 && (rc = ensure(P, kKV1, 2 * kv_half + 256))) return rc;
 
     // the previous call (maybe on another stream) may still be using the staging buffers
     if (P.used) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_last, 0));
@@ -138,66 +163,73 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     const uint8_t* hk = reinterpret_cast<const uint8_t*>(a.k);
     const uint8_t* hv = reinterpret_cast<const uint8_t*>(a.v);
     uint8_t* ho = reinterpret_cast<uint8_t*>(a.o);
-    int piece = 0;
+    int piece = 0, unit = 0;
     bool comp_used[2] = {false, false}, out_used[2] = {false, false}, kv_used[2] = {false, false};
     for (int b = 0; b < B; ++b) {
-        const int kvb = b & 1;
-        uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + kvb]);
-        uint8_t* dV = dK + ((size_t)Sk * kv_row + 255) / 256 * 256;
-        // the K/V buffer of entry b was last read by the kernels of entry b - 2
-        if (kv_used[kvb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb], 0));
-        int keys_up = 0;   // keys of this entry already on the device
-        for (int r = 0; r < n_r; ++r, ++piece) {
-            const int r0 = r * rows_per, r1 = Sq < r0 + rows_per ? Sq : r0 + rows_per, rows = r1 - r0;
-            int keys = a.causal ? r1 + shift : Sk;       // keys [0, keys) are visible to rows < r1
-            keys = keys < 0 ? 0 : (keys > Sk ? Sk : keys);
-            const int pb = piece & 1;
-            uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
-            uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
-            float* dL = reinterpret_cast<float*>(P.buf[kL0 + pb]);
-            // ---- upload: the piece's Q rows and the K/V rows it is the first to need
-            if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
-            if ((rc = copy_rows(dQ, q_row, hq + es * ((size_t)b * a.q_batch_stride + (size_t)r0 * a.q_row_stride),
-                                es * a.q_row_stride, q_row, rows, cudaMemcpyHostToDevice, P.s_in)))
-                return rc;
-            if (keys > keys_up) {
-                const size_t n = (size_t)(keys - keys_up);
-                if ((rc = copy_rows(dK + keys_up * kv_row, kv_row, hk + es * ((size_t)b * a.k_batch_stride + (size_t)keys_up * a.k_row_stride),
-                                    es * a.k_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)) ||
-                    (rc = copy_rows(dV + keys_up * kv_row, kv_row, hv + es * ((size_t)b * a.v_batch_stride + (size_t)keys_up * a.v_row_stride),
-                                    es * a.v_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)))
+        for (int g = 0; g < n_hg; ++g, ++unit) {
+            const int hk0 = g * hg, hkn = (Hkv - hk0 < hg) ? Hkv - hk0 : hg;      // kv-heads [hk0, hk0 + hkn)
+            const int hq0 = hk0 * grp, hqn = hkn * grp;
+            const size_t q_row = (size_t)hqn * D * es, kv_row = (size_t)hkn * D * es;
+            const int kvb = unit & 1;
+            uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + kvb]);
+            uint8_t* dV = dK + kv_half;
+            // this K/V buffer was last read by the kernels of the unit before the previous one
+            if (kv_used[kvb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb], 0));
+            int keys_up = 0;   // keys of this unit already on the device
+            for (int r = 0; r < n_r; ++r, ++piece) {
+                const int r0 = r * rows_per, r1 = Sq < r0 + rows_per ? Sq : r0 + rows_per, rows = r1 - r0;
+                int keys = a.causal ? r1 + shift : Sk;       // keys [0, keys) are visible to rows < r1
+                keys = keys < 0 ? 0 : (keys > Sk ? Sk : keys);
+                const int pb = piece & 1;
+                uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
+                uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
+                float* dL = reinterpret_cast<float*>(P.buf[kL0 + pb]);
+                // ---- upload: the piece's Q rows and the K/V rows it is the first to need
+                if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
+                if ((rc = copy_rows(dQ, q_row, hq + es * ((size_t)b * a.q_batch_stride + (size_t)r0 * a.q_row_stride + (size_t)hq0 * D),
+                                    es * a.q_row_stride, q_row, rows, cudaMemcpyHostToDevice, P.s_in)))
                     return rc;
-                keys_up = keys;
+                if (keys > keys_up) {
+                    const size_t n = (size_t)(keys - keys_up);
+                    if ((rc = copy_rows(dK + keys_up * kv_row, kv_row,
+                                        hk + es * ((size_t)b * a.k_batch_stride + (size_t)keys_up * a.k_row_stride + (size_t)hk0 * D),
+                                        es * a.k_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)) ||
+                        (rc = copy_rows(dV + keys_up * kv_row, kv_row,
+                                        hv + es * ((size_t)b * a.v_batch_stride + (size_t)keys_up * a.v_row_stride + (size_t)hk0 * D),
+                                        es * a.v_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)))
+                        return rc;
+                    keys_up = keys;
+                }
+                SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
+                // ---- kernel
+                SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
+                if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
+                sfa_fwd_args d = {};
+                d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
+                d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = hqn; d.heads_kv = hkn; d.head_dim = D;
+                d.q_batch_stride = (int64_t)rows * hqn * D; d.q_row_stride = (int64_t)hqn * D; d.q_head_stride = D;
+                d.k_batch_stride = (int64_t)Sk * hkn * D; d.k_row_stride = (int64_t)hkn * D; d.k_head_stride = D;
+                d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
+                d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
+                d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
+                if ((rc = launch_fwd(d, cur))) return rc;
+                SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
+                comp_used[pb] = true;
+                // ---- download
+                SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
+                if ((rc = copy_rows(ho + es * ((size_t)b * a.o_batch_stride + (size_t)r0 * a.o_row_stride + (size_t)hq0 * D),
+                                    es * a.o_row_stride, dO, q_row, q_row, rows, cudaMemcpyDeviceToHost, P.s_out)))
+                    return rc;
+                if (a.lse)   // host (batch, heads, Sq) fp32: one row of `rows` floats per head
+                    if ((rc = copy_rows(a.lse + ((size_t)b * Hq + hq0) * Sq + r0, (size_t)Sq * 4, dL, (size_t)rows * 4,
+                                        (size_t)rows * 4, hqn, cudaMemcpyDeviceToHost, P.s_out)))
+                        return rc;
+                SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
+                out_used[pb] = true;
             }
-            SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
-            // ---- kernel
-            SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
-            if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
-            sfa_fwd_args d = {};
-            d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
-            d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = Hq; d.heads_kv = Hkv; d.head_dim = D;
-            d.q_batch_stride = (int64_t)rows * Hq * D; d.q_row_stride = (int64_t)Hq * D; d.q_head_stride = D;
-            d.k_batch_stride = (int64_t)Sk * Hkv * D; d.k_row_stride = (int64_t)Hkv * D; d.k_head_stride = D;
-            d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
-            d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
-            d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
-            if ((rc = launch_fwd(d, cur))) return rc;
-            SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
-            comp_used[pb] = true;
-            // ---- download
-            SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
-            if ((rc = copy_rows(ho + es * ((size_t)b * a.o_batch_stride + (size_t)r0 * a.o_row_stride), es * a.o_row_stride,
-                                dO, q_row, q_row, rows, cudaMemcpyDeviceToHost, P.s_out)))
-                return rc;
-            if (a.lse)   // host (batch, heads, Sq) fp32: one row of `rows` floats per head
-                if ((rc = copy_rows(a.lse + ((size_t)b * Hq) * Sq + r0, (size_t)Sq * 4, dL, (size_t)rows * 4, (size_t)rows * 4,
-                                    Hq, cudaMemcpyDeviceToHost, P.s_out)))
-                    return rc;
-            SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
-            out_used[pb] = true;
+            SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb], cur));
+            kv_used[kvb] = true;
         }
-        SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb], cur));
-        kv_used[kvb] = true;
     }
     for (int i = 0; i < 2; ++i)
         if (out_used[i]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[i], 0));

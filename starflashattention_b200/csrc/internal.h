@@ -116,7 +116,7 @@ int fwd_error_flag_read_v1(int* value);
 int fwd_error_flag_clear_v1();
 // Tuning overrides of the prefill launcher, read from the environment once per process.
 struct FwdTuning {
-    int poly = -1, softrel = -1, stagger = -1, nq = 0, v1 = 0, group = 0, delay = -1, defer = -1, poll = 0;
+    int poly = -1, softrel = -1, stagger = -1, nq = 0, v1 = 0, group = 0, delay = -1, defer = -1, poll = 0, tail = -1;
 };
 const FwdTuning& fwd_tuning();
 // Two zeroed ints (next-item counter, CTAs done) for one launch of the persistent prefill kernel; the kernel
