@@ -24,7 +24,9 @@ LIB = os.path.join(PKG, "lib", "libStarFlashAttention.so")
 OBJ_PROBES = os.path.join(PKG, "lib", "obj_probes")
 LIB_PROBES = os.path.join(PKG, "lib", "libStarFlashAttention_probes.so")
 
-SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "fwd_sm100_v1.cu", "host_pipeline.cu", "capi.cu"]
+SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "host_pipeline.cu", "capi.cu"]
+# the probe library also carries the round-1 prefill kernel (one CTA per query block) for A/B runs: SFA_FWD_V1=1
+PROBE_SOURCES = SOURCES + ["fwd_sm100_v1.cu"]
 HEADERS = [os.path.join(CSRC, "internal.h"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(CSRC, "rope.cuh"), os.path.join(CSRC, "merge.cuh"),
            os.path.join(ROOT, "include", "star_flash_attn.h"), os.path.join(ROOT, "include", "src", "flash_attn.h"),
            os.path.join(ROOT, "include", "src", "params.h"), os.path.join(ROOT, "include", "src", "traits.h")]
@@ -66,12 +68,13 @@ def _compile(src: str, verbose: bool, probes: bool = False) -> str:
 def build(force: bool = False, verbose: bool = False, probes: bool = False) -> str:
     obj_dir, lib = (OBJ_PROBES, LIB_PROBES) if probes else (OBJ, LIB)
     os.makedirs(obj_dir, exist_ok=True)
-    todo = [s for s in SOURCES
+    sources = PROBE_SOURCES if probes else SOURCES
+    todo = [s for s in sources
             if force or _stale(os.path.join(obj_dir, s.replace(".cu", ".o")), [os.path.join(CSRC, s), *HEADERS])]
     if todo:
         with concurrent.futures.ThreadPoolExecutor(max_workers=len(todo)) as ex:
             list(ex.map(lambda s: _compile(s, verbose, probes), todo))
-    objs = [os.path.join(obj_dir, s.replace(".cu", ".o")) for s in SOURCES]
+    objs = [os.path.join(obj_dir, s.replace(".cu", ".o")) for s in sources]
     if force or todo or _stale(lib, objs):
         cmd = [nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib, *objs]
         r = subprocess.run(cmd, capture_output=True, text=True)

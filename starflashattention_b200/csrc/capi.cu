@@ -455,13 +455,17 @@ int sfa_fwd_watchdog(int clear) {
     int v = 0, v1 = 0;
     int rc = sfa::fwd_error_flag_read(&v);
     if (rc) return rc;
+#ifdef SFA_PROBES
     if ((rc = sfa::fwd_error_flag_read_v1(&v1))) return rc;
+#endif
     if (clear && v) {
         // an aborted persistent kernel may have left its schedule counters behind
         if ((rc = sfa::fwd_error_flag_clear())) return rc;
         rc = sfa::fwd_sched_reset();
     }
+#ifdef SFA_PROBES
     if (clear && v1) rc = sfa::fwd_error_flag_clear_v1();
+#endif
     return rc ? rc : (v ? v : v1);
 }
 

@@ -1105,7 +1105,9 @@ int launch_fwd(const sfa_fwd_args& a, cudaStream_t stream) {
         if (x % 16) return fail(SFA_ERR_INVALID, "fwd: tensor base pointers must be 16-byte aligned");
     if (a.batch == 0 || a.seqlen_q == 0) return SFA_OK;
     const FwdTuning& tune = fwd_tuning();
-    if (tune.v1) return launch_fwd_v1(a, stream);
+#ifdef SFA_PROBES
+    if (tune.v1) return launch_fwd_v1(a, stream);   // the round-1 kernel (one CTA per query block), A/B runs only
+#endif
     const DeviceInfo* dev = current_device();
     if (!dev) return SFA_ERR_NO_DEVICE;
 
