@@ -610,6 +610,13 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
             // one wave is also the best two-launch count while it means at most ~24 splits (32 units: 16 - 18 splits
             // 58 us at 16k keys and 99 us at 32k, against 62 and 101 us for the 56 of the rule below)
             if (one_wave <= 24 && s > one_wave) return (int)(one_wave < by_len ? one_wave : by_len);
+            // ... and for very few units with a long cache (one sequence: 8 units, 74 splits each fill the 592 CTA slots
+            // once): under ncu the split kernel takes 25.3 us with 72 splits against 28.1 - 28.5 with 48 or 128 and 32.9
+            // with 96 (1.3 waves); the combine kernel costs 6 us either way (profiles/r2_fwd_tuning.md section 7)
+            if (one_wave <= 96 && s > one_wave) {
+                const long w = one_wave / 8 * 8;   // whole 8s: even chunks
+                return (int)(w < by_len ? w : by_len);
+            }
         }
     }
     return (int)s;

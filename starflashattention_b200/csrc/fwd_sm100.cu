@@ -297,7 +297,7 @@ __device__ __forceinline__ Item decode_item(const FwdParams& p, int idx) {
 }
 
 // BF16: data type (false = fp16).  POLY: of every 8 column pairs, how many take the polynomial exp2.
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, bool POLYSCALAR>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, int POLYSCALAR>
 __global__ void __launch_bounds__(FwdRegs<NQ>::kThreads, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CUtensorMap k_map,
            const __grid_constant__ CUtensorMap v_map, const __grid_constant__ CUtensorMap o_map, const FwdParams p) {
@@ -843,8 +843,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap q_map, const __grid_constant__ CU
                         unpack_f2(xq[i % kAhead], x0, x1);
                         if (i + kAhead < kPairs) xq[i % kAhead] = scale(i + kAhead);
                         uint64_t e;
-                        if ((i & 7) >= 8 - kPoly) {
-                            if constexpr (POLYSCALAR) e = pack_f2(exp2_poly1(x0), exp2_poly1(x1));
+                        // which pairs take the polynomial: POLYSCALAR 0 / 1: the last kPoly of every 8 (a block);
+                        // 2 / 3: spread, every (8 / kPoly)-th pair; odd values: scalar arithmetic
+                        const bool on_poly = kPoly > 0 && ((POLYSCALAR < 2) ? ((i & 7) >= 8 - kPoly)
+                                                                           : ((i % (8 / (kPoly > 0 ? kPoly : 1))) == (8 / (kPoly > 0 ? kPoly : 1)) - 1));
+                        if (on_poly) {
+                            if constexpr ((POLYSCALAR & 1) != 0) e = pack_f2(exp2_poly1(x0), exp2_poly1(x1));
                             else e = exp2_poly2(x0, x1);
                         } else {
                             p0 = ex2_v(x0); p1 = ex2_v(x1);
@@ -954,7 +958,7 @@ struct FwdMaps {
     alignas(64) CUtensorMap q, k, v, o;
 };
 
-template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, bool POLYSCALAR>
+template <int D, int NQ, int NSTAGE, bool BF16, int POLY, int EXPDELAY, bool DEFER, int POLL, int POLYSCALAR>
 int launch_instance(const FwdMaps& m, FwdParams p, int batch, int sm_count, cudaStream_t stream) {
     using L = FwdSmem<D, NQ, NSTAGE>;
     auto kern = fwd_kernel<D, NQ, NSTAGE, BF16, POLY, EXPDELAY, DEFER, POLL, POLYSCALAR>;
@@ -1022,27 +1026,35 @@ int launch_dtype(const FwdMaps& m, const FwdParams& p, int batch, int head_dim, 
     // DELAY (pairs between a pair's MUFUs and its consumers in the exp2 loop) and DEFER (epilogue inside the next
     // item's first tile) as measured on C3 / C2 (profiles/r2_fwd_tuning.md): 2 / 0 pairs, not deferred.
     if (head_dim == 128) {
-        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, false, 0, false);
+        if (nq == 1) SFA_LAUNCH(128, 1, 4, 0, 2, false, 0, 0);
 #ifdef SFA_PROBES
-        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, false);
-        if (tune.poly == 12) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, true);
-        if (tune.poly == 11) SFA_LAUNCH(128, 2, 4, 1, 2, false, 0, true);
-        if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true, 0, false);
-        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, false, 0, false);
-        if (tune.poll == 1) SFA_LAUNCH(128, 2, 4, 0, 2, false, 1, false);
+        if (tune.poly == 2) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, 0);
+        if (tune.poly == 12) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, 1);
+        if (tune.poly == 11) SFA_LAUNCH(128, 2, 4, 1, 2, false, 0, 1);
+        if (tune.defer == 1) SFA_LAUNCH(128, 2, 4, 0, 2, true, 0, 0);
+        if (tune.poly == 32) SFA_LAUNCH(128, 2, 4, 2, 2, false, 0, 3);
+        if (tune.poly == 31) SFA_LAUNCH(128, 2, 4, 1, 2, false, 0, 3);
+        if (tune.delay == 0) SFA_LAUNCH(128, 2, 4, 0, 0, false, 0, 0);
+        if (tune.poll == 1) SFA_LAUNCH(128, 2, 4, 0, 2, false, 1, 0);
 #endif
-        SFA_LAUNCH(128, 2, 4, 0, 2, false, 0, false);
+        SFA_LAUNCH(128, 2, 4, 0, 2, false, 0, 0);
     }
-    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, false, 0, false);
+    if (nq == 1) SFA_LAUNCH(64, 1, 6, 0, 0, false, 0, 0);
 #ifdef SFA_PROBES
-    if (tune.poly == 0) SFA_LAUNCH(64, 2, 6, 0, 0, false, 0, false);
-    if (tune.poly == 12) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, true);
-    if (tune.poly == 13) SFA_LAUNCH(64, 2, 6, 3, 0, false, 0, true);
-    if (tune.defer == 1) SFA_LAUNCH(64, 2, 6, 2, 0, true, 0, false);
+    if (tune.poly == 2) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, 0);
+    if (tune.poly == 12) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, 1);
+    if (tune.poly == 13) SFA_LAUNCH(64, 2, 6, 3, 0, false, 0, 1);
+    if (tune.defer == 1) SFA_LAUNCH(64, 2, 6, 2, 0, true, 0, 0);
+    if (tune.poly == 22) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, 2);   // packed, spread
+    if (tune.poly == 32) SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, 3);   // scalar, spread
+    if (tune.poly == 34) SFA_LAUNCH(64, 2, 6, 4, 0, false, 0, 3);   // scalar, spread, every second pair
+    if (tune.poly == 31) SFA_LAUNCH(64, 2, 6, 1, 0, false, 0, 3);   // scalar, one pair of 8
 #endif
-    // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time): a quarter of the exponentials go to
-    // the FMA-pipe polynomial (measured on C2: 0.404 -> 0.390 ms)
-    SFA_LAUNCH(64, 2, 6, 2, 0, false, 0, false);
+    // head_dim 64 is MUFU-bound (a tile's exp2 takes twice its MMA time).  In the round-1 kernel a quarter of the
+    // exponentials on the FMA-pipe polynomial paid (0.404 -> 0.390 ms on C2); in the persistent kernel no share and no
+    // arrangement of it does (none 0.399, 2/8 packed 0.413, 2/8 scalar spread 0.408, 1/8 0.423, 4/8 0.537 ms), although
+    // the loop in isolation gains 14 % (tools/micro/exp_poly.cu) - profiles/r2_fwd_tuning.md.  MUFU only.
+    SFA_LAUNCH(64, 2, 6, 0, 0, false, 0, 0);
 #undef SFA_LAUNCH
 }
 
