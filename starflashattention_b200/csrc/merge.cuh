@@ -34,9 +34,18 @@ __device__ __forceinline__ void merge_splits(const float* __restrict__ o_part, c
                                              int64_t row0, int S, float* w_sm, MergeScratch<D>& sc, float& acc,
                                              float& L, float& M) {
     constexpr int T = D * kMergeGroups, W = T / 32;
+    constexpr int G = kMergeGroups;
+    constexpr int kPre = 8;               // partial rows per thread whose loads go out before the weights are known
     const int tid = threadIdx.x, g = tid / D, d = tid - g * D, warp = tid >> 5, lane = tid & 31;
-    float m = -INFINITY;
-    for (int s = tid; s < S; s += T) m = fmaxf(m, ml_part[row0 + s].x);
+    // One global round trip instead of three: every (m, l) is read once (S <= T: at most one per thread, more only in
+    // the fallback loop), and the first kPre * G rows of o_part are requested before M and the weights exist.
+    const float* op = o_part + row0 * D + d;
+    const float2 ml0 = tid < S ? ml_part[row0 + tid] : make_float2(-INFINITY, 0.f);
+    float v[kPre];
+#pragma unroll
+    for (int i = 0; i < kPre; ++i) v[i] = (g + i * G < S) ? op[(int64_t)(g + i * G) * D] : 0.f;
+    float m = ml0.x;
+    for (int s = tid + T; s < S; s += T) m = fmaxf(m, ml_part[row0 + s].x);
     m = warp_max(m);
     if (lane == 0) sc.red[warp] = m;
     __syncthreads();
@@ -44,7 +53,12 @@ __device__ __forceinline__ void merge_splits(const float* __restrict__ o_part, c
     M = warp_max(m);
     __syncthreads();
     float l = 0.f;
-    for (int s = tid; s < S; s += T) {
+    if (tid < S) {
+        const float w = (ml0.x == -INFINITY) ? 0.f : exp2f(ml0.x - M);
+        w_sm[tid] = w;
+        l = w * ml0.y;
+    }
+    for (int s = tid + T; s < S; s += T) {
         const float2 ml = ml_part[row0 + s];
         const float w = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - M);
         w_sm[s] = w;
@@ -55,11 +69,14 @@ __device__ __forceinline__ void merge_splits(const float* __restrict__ o_part, c
     __syncthreads();                      // also publishes w_sm
     l = lane < W ? sc.red[lane] : 0.f;
     L = warp_sum(l);
-    // four independent loads in flight per thread: with a few hundred splits the loop is latency bound
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    const float* op = o_part + row0 * D + d;
-    constexpr int G = kMergeGroups;
-    int s = g;
+#pragma unroll
+    for (int i = 0; i < kPre; i += 2) {
+        if (g + i * G < S) a0 += w_sm[g + i * G] * v[i];
+        if (g + (i + 1) * G < S) a1 += w_sm[g + (i + 1) * G] * v[i + 1];
+    }
+    // the rest, four independent loads in flight per thread
+    int s = g + kPre * G;
     for (; s + 3 * G < S; s += 4 * G) {
         const float v0 = op[(int64_t)s * D], v1 = op[(int64_t)(s + G) * D];
         const float v2 = op[(int64_t)(s + 2 * G) * D], v3 = op[(int64_t)(s + 3 * G) * D];
