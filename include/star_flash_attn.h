@@ -72,7 +72,8 @@ int sfa_fwd(const sfa_fwd_args* args, void* stream);
  * One query token per sequence.  q (batch, heads_q, head_dim); k_cache/v_cache
  * (batch, max_len, heads_kv, head_dim) addressed through element strides; seqlens int32
  * (batch) = number of visible keys per sequence (NULL => seqlen_k for all); o like q;
- * lse (batch, heads_q) fp32 or NULL.  heads_q / heads_kv in {1,2,4,8}.
+ * lse (batch, heads_q) fp32 or NULL.  heads_q % heads_kv == 0; a GQA group of up to 8 query heads
+ * shares one pass over K/V, a larger group (MQA with 16, 32 ... heads) is served in equal chunks of <= 8.
  * num_splits <= 0 lets the launcher choose.  workspace: device scratch of at least
  * sfa_decode_workspace_bytes(...) bytes, or NULL to use the library's per-device grow-only
  * buffer (grown with cudaMalloc outside graph capture only). */

@@ -61,7 +61,7 @@ int decode_impl(const sfa_decode_args& a, int seqlen_add, cudaStream_t stream, c
     L.o_bs = a.o_batch_stride; L.o_hs = a.o_head_stride;
     L.scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
     L.seqlen_add = seqlen_add;
-    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv, a.seqlen_k + seqlen_add, dev->sm_count);
+    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv * decode_head_chunks(a.heads_q, a.heads_kv), a.seqlen_k + seqlen_add, dev->sm_count);
     L.dtype = a.dtype;
     L.o_part = nullptr; L.ml_part = nullptr;
     if (fused) {
@@ -210,7 +210,7 @@ int shard_local_pass(const sfa_decode_args& a, int rank, int world, ShardLaunch&
     L.o_bs = a.o_batch_stride; L.o_hs = a.o_head_stride;
     L.scale = a.softmax_scale > 0.f ? a.softmax_scale : 1.f / sqrtf((float)a.head_dim);
     L.seqlen_add = 0;
-    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv, a.seqlen_k, dev->sm_count);
+    L.num_splits = resolve_splits(a.num_splits, a.batch, a.heads_kv * decode_head_chunks(a.heads_q, a.heads_kv), a.seqlen_k, dev->sm_count);
     L.dtype = a.dtype;
     L.force_partials = true;
     const size_t rows = (size_t)a.batch * a.heads_q * L.num_splits;
@@ -320,7 +320,8 @@ int sfa_decode_num_splits(const sfa_decode_args* args) {
     if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_decode_num_splits: null args");
     const sfa::DeviceInfo* dev = sfa::current_device();
     if (!dev) return SFA_ERR_NO_DEVICE;
-    return sfa::resolve_splits(args->num_splits, args->batch, args->heads_kv, args->seqlen_k, dev->sm_count);
+    return sfa::resolve_splits(args->num_splits, args->batch, args->heads_kv * sfa::decode_head_chunks(args->heads_q, args->heads_kv), args->seqlen_k,
+                               dev->sm_count);
 }
 
 size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits) {

@@ -11,7 +11,9 @@
 //
 // Work decomposition: grid (num_splits, heads_kv, batch), 4 warps per CTA.  A CTA owns one
 // contiguous chunk of one kv-head's keys and serves all heads_q/heads_kv query heads of its GQA
-// group, so K/V are read once per group.  Inside the CTA the warps take 16-key steps round robin;
+// group, so K/V are read once per group (a group of more than 8 query heads - MQA with 16 or 32 heads - is cut
+// into equal chunks of <= 8, one CTA row each: grid.y = heads_kv * chunks, K/V read once per chunk).
+// Inside the CTA the warps take 16-key steps round robin;
 // each warp keeps a private online-softmax state (m, l, O) and the four states are merged through
 // shared memory at the end.
 //
@@ -103,6 +105,7 @@ struct DecodeParams {
     const void* sin_table;
     int64_t qkv_stride;
     int rotary_dim, heads_kv;
+    int kv_chunks;        // CTAs along grid.y per kv head: a GQA group of more than 8 query heads is served in chunks of `group`
     int force_partials;
     // paged cache (PAGED kernels only): k / v are page pools (pages, page_size, heads_kv, D) with k_bs / v_bs the
     // page stride; block_table[b * bt_stride + i] is the pool page holding keys [i, i + 1) << page_shift of sequence b
@@ -157,6 +160,8 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane >> 2, t = lane & 3;
     const int g = p.group;
+    // grid.y counts chunks of <= 8 query heads; chunk hk serves query heads [hk * g, hk * g + g) and reads kv head hkv
+    const int hkv = p.kv_chunks == 1 ? hk : hk / p.kv_chunks;
 
     const int pos = p.seqlens ? p.seqlens[b] : p.seqlen_k;   // FUSED: row the new token is appended at
     int len = pos + p.seqlen_add;
@@ -205,8 +210,8 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     float l_run = 0.f;         // this thread's share of the denominator
     float m_run1 = -INFINITY, l_run1 = 0.f;   // SWAP only: head 2t + 1
 
-    const T* kbase = reinterpret_cast<const T*>(p.k) + (PAGED ? 0 : (int64_t)b * p.k_bs) + (int64_t)hk * p.k_hs;
-    const T* vbase = reinterpret_cast<const T*>(p.v) + (PAGED ? 0 : (int64_t)b * p.v_bs) + (int64_t)hk * p.v_hs;
+    const T* kbase = reinterpret_cast<const T*>(p.k) + (PAGED ? 0 : (int64_t)b * p.k_bs) + (int64_t)hkv * p.k_hs;
+    const T* vbase = reinterpret_cast<const T*>(p.v) + (PAGED ? 0 : (int64_t)b * p.v_bs) + (int64_t)hkv * p.v_hs;
     const int32_t* bt = PAGED ? p.block_table + (int64_t)b * p.bt_stride : nullptr;
 
     // One 16-key step of this warp.  NEW (fused step only): the step holds the appended token, whose k (rotated
@@ -215,8 +220,8 @@ __global__ void __launch_bounds__(kWarps * 32, SWAP ? 4 : 3) decode_splitkv_kern
     auto step = [&](const int base, auto new_tag) {
         constexpr bool NEW = decltype(new_tag)::value;
         const int last = k_end - 1;
-        const T* tok_k = NEW ? token_row(p.heads_q + hk) : nullptr;
-        const T* tok_v = NEW ? token_row(p.heads_q + p.heads_kv + hk) : nullptr;
+        const T* tok_k = NEW ? token_row(p.heads_q + hkv) : nullptr;
+        const T* tok_v = NEW ? token_row(p.heads_q + p.heads_kv + hkv) : nullptr;
         // rows of this step: cache row `key` is kb + (key - key0) * k_rs (paged: inside the step's page)
         const T* kb = kbase;
         const T* vb = vbase;
@@ -530,7 +535,7 @@ int launch_ex(K kern, dim3 grid, int threads, size_t smem, int cluster, bool pdl
 
 template <typename T, int D>
 int launch_typed(const DecodeLaunch& a, const DecodeParams& p, cudaStream_t stream) {
-    const dim3 grid(a.num_splits, a.heads_kv, a.batch);
+    const dim3 grid(a.num_splits, a.heads_kv * p.kv_chunks, a.batch);
     const int threads = kWarps * 32;
     const bool pdl_all = decode_pdl_level() >= 2;
     if (a.num_splits >= 2 && a.num_splits <= kMaxClusterSplits && !a.force_partials && decode_cluster_enabled() &&
@@ -588,6 +593,14 @@ DecodeTuning& decode_tuning() {
     return t;
 }
 
+int decode_head_chunks(int heads_q, int heads_kv) {
+    if (heads_kv <= 0 || heads_q < heads_kv) return 1;
+    const int g = heads_q / heads_kv;
+    int chunks = (g + 7) / 8;
+    while (chunks < g && g % chunks != 0) ++chunks;
+    return chunks;
+}
+
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) {
     const int waves = decode_tuning().waves > 0 ? decode_tuning().waves : 4;
     const long units = (long)batch * heads_kv;
@@ -630,8 +643,11 @@ size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_spli
 
 int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     if (a.heads_kv <= 0 || a.heads_q % a.heads_kv != 0) return fail(SFA_ERR_INVALID, "heads_q must be a multiple of heads_kv");
-    const int g = a.heads_q / a.heads_kv;
-    if (g > 8) return fail(SFA_ERR_UNSUPPORTED, "decode supports heads_q / heads_kv <= 8");
+    // One CTA serves up to 8 query heads (the 8 columns of its MMAs).  A larger GQA / MQA group is cut into equal chunks
+    // of <= 8 heads, each a CTA row of its own over the same kv head: K/V are then read once per chunk.
+    const int chunks = decode_head_chunks(a.heads_q, a.heads_kv);
+    const int g = a.heads_q / a.heads_kv / chunks;
+    if ((long)a.heads_kv * chunks > 65535) return fail(SFA_ERR_UNSUPPORTED, "decode: more than 65535 head chunks");
     if (a.head_dim != 64 && a.head_dim != 128) return fail(SFA_ERR_UNSUPPORTED, "head_dim must be 64 or 128");
     if (a.batch == 0) return SFA_OK;
     if (a.block_table) {
@@ -647,7 +663,7 @@ int launch_decode(const DecodeLaunch& a, cudaStream_t stream) {
     p.num_splits = a.num_splits;
     p.scale_log2 = a.scale * kLog2e;
     p.qkv = a.fused_qkv; p.cos_table = a.cos_table; p.sin_table = a.sin_table; p.qkv_stride = a.qkv_stride;
-    p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv; p.force_partials = a.force_partials ? 1 : 0;
+    p.rotary_dim = a.rotary_dim; p.heads_kv = a.heads_kv; p.kv_chunks = chunks; p.force_partials = a.force_partials ? 1 : 0;
     p.block_table = a.block_table; p.bt_stride = a.bt_stride; p.page_shift = 0;
     while (a.block_table && (1 << p.page_shift) < a.page_size) ++p.page_shift;
     if (a.dtype == SFA_FP16) {

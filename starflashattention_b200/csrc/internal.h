@@ -74,6 +74,9 @@ struct DecodeLaunch {
     int64_t bt_stride = 0;
     int page_size = 0;
 };
+// CTA rows per kv head: 1 while the GQA group has at most 8 query heads, else the smallest count of equal chunks of <= 8.
+int decode_head_chunks(int heads_q, int heads_kv);
+// `heads_kv` counts head chunks (heads_kv * decode_head_chunks(...)).
 int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count);
 size_t decode_workspace_bytes(int batch, int heads_q, int head_dim, int num_splits);
 int launch_decode(const DecodeLaunch& p, cudaStream_t stream);

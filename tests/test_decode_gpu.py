@@ -42,6 +42,11 @@ def _rand(shape, dtype, seed, scale=1.0):
     (2, 4, 2, 64, 513, [513, 17], 3),          # head_dim 64
     (2, 2, 2, 128, 256, [0, 256], 4),          # an empty sequence: O = 0, LSE = -inf
     (1, 32, 8, 128, 4096, [4096], 0),          # the C4 head layout at a CPU-checkable length
+    (2, 32, 2, 128, 777, [777, 300], 0),       # GQA 16: two chunks of 8 query heads per kv head
+    (1, 16, 1, 64, 1500, [1500], 6),           # MQA 16 at head_dim 64, cluster-sized split count
+    (2, 24, 2, 128, 520, [100, 520], 3),       # GQA 12: two chunks of 6
+    (1, 32, 1, 128, 2048, [2000], 0),          # MQA 32: four chunks of 8
+    (1, 11, 1, 128, 300, [300], 2),            # a prime group above 8: eleven chunks of one head
 ])
 def test_decode_matches_oracle(dtype, B, Hq, Hkv, D, M, lens, splits):
     import starflashattention_b200 as sfa
@@ -124,6 +129,7 @@ def _paged_case(dtype, B, Hkv, D, page, blocks, seed):
     (2, 4, 2, 64, 128, 5, [513, 17], 3),         # head_dim 64
     (2, 2, 2, 128, 256, 2, [0, 512], 4),         # an empty sequence; chunk (64) smaller than the page
     (1, 32, 8, 128, 256, 16, [4096], 0),         # the C4 head layout
+    (2, 16, 1, 128, 32, 20, [640, 35], 4),       # MQA 16 (two chunks of 8 query heads) over pages
 ])
 def test_decode_paged_matches_oracle_and_dense_kernel(dtype, B, Hq, Hkv, D, page, blocks, lens, splits):
     """Paged cache (scope row f1): against the oracle over the gathered cache, and bit for bit against the dense
@@ -201,7 +207,8 @@ def test_decode_paged_full_c4_shape_equals_dense():
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("Hq,Hkv,D,page,use_tables", [(8, 2, 128, 64, True), (4, 4, 128, 16, False), (8, 1, 64, 128, True)])
+@pytest.mark.parametrize("Hq,Hkv,D,page,use_tables", [(8, 2, 128, 64, True), (4, 4, 128, 16, False), (8, 1, 64, 128, True),
+                                                     (32, 2, 128, 64, True)])   # GQA 16: both chunks append the same row
 def test_decoder_step_paged_matches_oracle_and_appends_into_the_page(dtype, Hq, Hkv, D, page, use_tables):
     """Fused RoPE + append + attention over a paged cache with GQA: positions at a page start, a page end, mid-page
     and on an empty sequence; the appended rows land in the page the block table names and nothing else changes."""
