@@ -101,6 +101,21 @@ int sfa_decode(const sfa_decode_args* args, void* stream);
 int sfa_decode_num_splits(const sfa_decode_args* args);
 size_t sfa_decode_workspace_bytes(int32_t batch, int32_t heads_q, int32_t head_dim, int32_t num_splits);
 
+/* Split-KV decode that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid allocation).  Same arguments, arithmetic and results as sfa_decode (args->workspace and
+ * args->workspace_bytes are ignored); the per-split partials live in ONE static device array of
+ * SFA_DECODE_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit, so the call makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  Limits: a launch whose partials
+ * (sfa_decode_workspace_bytes(batch, heads_q, head_dim, sfa_decode_num_splits(args)) bytes) exceed the array returns
+ * SFA_ERR_INVALID with the size it needs - lower num_splits or the batch, or use sfa_decode with a workspace.  Every
+ * call on a device shares the array: calls that OVERLAP on the GPU (two streams, concurrently replayed graphs) race
+ * on it; calls ordered on one stream do not.  The array keeps the last call's contents; nothing in it needs to start
+ * at zero (every split writes its own partial before the combine kernel reads it). */
+#define SFA_DECODE_STATIC_SCRATCH_BYTES (16u << 20)
+int sfa_decode_static(const sfa_decode_args* args, void* stream);
+size_t sfa_decode_static_scratch_bytes(void);
+
 /* ---------------------------------------------------------------- split-KV decode over a paged cache ---
  * Row f1 of the scope table ("a paged/strided KV-cache layout"); the reference documents one
  * dense (batch, layer, max_len, heads, head_dim) cache (src/params.h:22-25) and has no paged form.

@@ -18,7 +18,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_workspace_bytes", "sfa_decoder_step_paged",
+    "sfa_fwd", "sfa_decode", "sfa_decode_static", "sfa_decode_static_scratch_bytes", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_workspace_bytes", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces", "sfa_tuning_set",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -125,6 +125,10 @@ def _load() -> C.CDLL:
     lib.sfa_fwd.restype = C.c_int
     lib.sfa_decode.argtypes = [C.POINTER(DecodeArgs), C.c_void_p]
     lib.sfa_decode.restype = C.c_int
+    lib.sfa_decode_static.argtypes = [C.POINTER(DecodeArgs), C.c_void_p]
+    lib.sfa_decode_static.restype = C.c_int
+    lib.sfa_decode_static_scratch_bytes.argtypes = []
+    lib.sfa_decode_static_scratch_bytes.restype = C.c_size_t
     lib.sfa_decode_paged.argtypes = [C.POINTER(DecodePagedArgs), C.c_void_p]
     lib.sfa_decode_paged.restype = C.c_int
     lib.sfa_fwd_host.argtypes = [C.POINTER(FwdHostArgs), C.c_void_p]

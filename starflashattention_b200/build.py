@@ -24,7 +24,7 @@ LIB = os.path.join(PKG, "lib", "libStarFlashAttention.so")
 OBJ_PROBES = os.path.join(PKG, "lib", "obj_probes")
 LIB_PROBES = os.path.join(PKG, "lib", "libStarFlashAttention_probes.so")
 
-SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "host_pipeline.cu", "capi.cu"]
+SOURCES = ["common.cu", "decode_sm100.cu", "rope_cache.cu", "shard_sm100.cu", "fwd_sm100.cu", "host_pipeline.cu", "capi.cu", "decode_static.cu"]
 # the probe library also carries the round-1 prefill kernel (one CTA per query block) for A/B runs: SFA_FWD_V1=1
 PROBE_SOURCES = SOURCES + ["fwd_sm100_v1.cu"]
 HEADERS = [os.path.join(CSRC, "internal.h"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(CSRC, "rope.cuh"), os.path.join(CSRC, "merge.cuh"),
