@@ -255,8 +255,10 @@ int sfa_fill(void* array, float value, int64_t n, int32_t dtype, void* stream);
  * Every pointer of `t` is a host pointer; strides are in elements and describe the HOST tensors (a caller may pass a
  * slice of the heads of a larger tensor: head stride must equal head_dim, batch / row strides are free); lse is
  * (batch, heads_q, seqlen_q) resp. (batch, heads_q) fp32 contiguous or NULL.  pieces <= 0: library's choice
- * (about 32 for prefill: (batch entry, block of query rows); 8 for decode: batch ranges).  Device staging is
- * owned by the library (grow-only, per device; released by sfa_release_workspaces).  Not graph-capturable. */
+ * (prefill: about 8 large (batch entry, kv-head group, block of query rows) pieces, plus geometrically smaller ones
+ * at the end of the call when the kernels are short beside the copies; 8 for decode: batch ranges); pieces > 0: that
+ * many uniform pieces.  Device staging is owned by the library (grow-only rings, per device; released by
+ * sfa_release_workspaces).  Not graph-capturable. */
 typedef struct sfa_fwd_host_args {
     sfa_fwd_args t;
     int32_t pieces;
@@ -268,6 +270,16 @@ typedef struct sfa_decode_host_args {
     int32_t pieces;
 } sfa_decode_host_args;
 int sfa_decode_host(const sfa_decode_host_args* args, void* stream);
+/* The piece plan sfa_fwd_host would follow for `args` (only the dimensions, `causal` and `pieces` are read; no device
+ * is needed): writes up to `capacity` pieces of 6 ints each - batch entry, first kv-head, kv-heads, first row, end
+ * row, unit (pieces of one unit share its K/V staging) - in issue order and returns the number of pieces of the plan. */
+int32_t sfa_fwd_host_plan(const sfa_fwd_host_args* args, int32_t* pieces, int32_t capacity);
+/* Diagnostics: number of pieces the most recent sfa_fwd_host call of this process was cut into. */
+int32_t sfa_fwd_host_last_pieces(void);
+/* Diagnostics (after sfa_tuning_set("host_trace", 1)): synchronises the device and writes, for up to `capacity`
+ * pieces of the last sfa_fwd_host call on the current device, 5 floats - milliseconds from the first upload's start
+ * to the piece's upload start, upload end, kernel start, kernel end, download end; returns the number of pieces. */
+int32_t sfa_fwd_host_trace(float* ms, int32_t capacity);
 
 /* ---------------------------------------------------------------- misc ---------------------- */
 /* Pitched copy between pinned host memory and the device on `stream` (cudaMemcpy2DAsync): `height` rows of
@@ -291,7 +303,10 @@ int sfa_fwd_probe_read(uint64_t* out, int32_t n);
 /* Test / tuning aid: sets one of the library's A-B switches for the rest of the process (they start from the
  * SFA_* environment variables, read once): "decode_cluster" (1: 2..8 splits merge in a thread-block cluster; 0:
  * partials + combine launch), "decode_pdl" (0..2), "decode_waves", "decode_ctas", "decoder_fused" (1: RoPE +
- * append inside the decode kernel; 0: stand-alone kernel first), "decode_swap" (0 in the probe build only).
+ * append inside the decode kernel; 0: stand-alone kernel first), "decode_swap" (0 in the probe build only),
+ * "host_taper" (0: sfa_fwd_host cuts uniform pieces only), "host_heavy" (-1 auto / 0 / 1: plan the call as one whose
+ * kernels are short / as long as its copies), "host_taper_bytes" (smallest refined piece, default 4 MiB),
+ * "host_piece_bytes" (the default plan has at most input bytes / this many pieces, default 8 MiB), "host_trace".
  * None of them changes the arithmetic contract; not thread-safe against concurrent launches. */
 int sfa_tuning_set(const char* name, int32_t value);
 /* Releases the per-device workspaces (synchronises the device). */

@@ -18,7 +18,7 @@ SFA_OK, SFA_ERR_INVALID, SFA_ERR_UNSUPPORTED, SFA_ERR_CUDA, SFA_ERR_NO_DEVICE = 
 
 # Every symbol include/star_flash_attn.h declares; tests check the library exports all of them.
 EXPORTED_SYMBOLS = (
-    "sfa_fwd", "sfa_decode", "sfa_decode_static", "sfa_decode_static_scratch_bytes", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_workspace_bytes", "sfa_decoder_step_paged",
+    "sfa_fwd", "sfa_decode", "sfa_decode_static", "sfa_decode_static_scratch_bytes", "sfa_decode_paged", "sfa_fwd_host", "sfa_decode_host", "sfa_fwd_host_plan", "sfa_fwd_host_last_pieces", "sfa_fwd_host_trace", "sfa_copy_2d", "sfa_decode_num_splits", "sfa_decode_workspace_bytes", "sfa_decoder_step", "sfa_decoder_step_workspace_bytes", "sfa_decoder_step_paged",
     "sfa_rotary_table", "sfa_fill", "sfa_last_error", "sfa_abi_version", "sfa_launch_count",
     "sfa_fwd_watchdog", "sfa_fwd_probe_read", "sfa_release_workspaces", "sfa_tuning_set",
     "sfa_decode_sharded", "sfa_decode_sharded_emulated", "sfa_shard_merge", "sfa_shard_workspace_bytes", "sfa_peer_alloc", "sfa_peer_open",
@@ -135,6 +135,12 @@ def _load() -> C.CDLL:
     lib.sfa_fwd_host.restype = C.c_int
     lib.sfa_decode_host.argtypes = [C.POINTER(DecodeHostArgs), C.c_void_p]
     lib.sfa_decode_host.restype = C.c_int
+    lib.sfa_fwd_host_plan.argtypes = [C.POINTER(FwdHostArgs), C.POINTER(C.c_int32), C.c_int32]
+    lib.sfa_fwd_host_plan.restype = C.c_int32
+    lib.sfa_fwd_host_last_pieces.argtypes = []
+    lib.sfa_fwd_host_last_pieces.restype = C.c_int32
+    lib.sfa_fwd_host_trace.argtypes = [C.POINTER(C.c_float), C.c_int32]
+    lib.sfa_fwd_host_trace.restype = C.c_int32
     lib.sfa_copy_2d.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p]
     lib.sfa_copy_2d.restype = C.c_int
     lib.sfa_decode_num_splits.argtypes = [C.POINTER(DecodeArgs)]

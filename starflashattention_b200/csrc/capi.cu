@@ -303,6 +303,22 @@ int sfa_decode_host(const sfa_decode_host_args* args, void* stream) {
     return sfa::decode_host_impl(args->t, args->pieces, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int32_t sfa_fwd_host_last_pieces(void) { return sfa::host_last_plan_pieces(); }
+int32_t sfa_fwd_host_trace(float* ms, int32_t capacity) { return sfa::fwd_host_trace(ms, capacity); }
+
+int32_t sfa_fwd_host_plan(const sfa_fwd_host_args* args, int32_t* pieces, int32_t capacity) {
+    if (!args) return sfa::fail(SFA_ERR_INVALID, "sfa_fwd_host_plan: null args");
+    const sfa_fwd_args& t = args->t;
+    const std::vector<sfa::HostPiece> plan =
+        sfa::plan_fwd_host(t.batch, t.seqlen_q, t.seqlen_k, t.heads_q, t.heads_kv, t.head_dim, t.causal != 0, args->pieces);
+    for (size_t i = 0; i < plan.size() && pieces && (int32_t)i < capacity; ++i) {
+        const sfa::HostPiece& pc = plan[i];
+        const int32_t row[6] = {pc.b, pc.hk0, pc.hkn, pc.r0, pc.r1, pc.unit};
+        for (int j = 0; j < 6; ++j) pieces[6 * i + j] = row[j];
+    }
+    return (int32_t)plan.size();
+}
+
 int sfa_copy_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes, size_t height,
                 int32_t kind, void* stream) {
     if (!dst || !src) return sfa::fail(SFA_ERR_INVALID, "sfa_copy_2d: null pointer");
@@ -439,6 +455,11 @@ int sfa_tuning_set(const char* name, int32_t value) {
     else if (k == "decode_waves") t.waves = value;
     else if (k == "decode_ctas") t.ctas_per_sm = value;
     else if (k == "decoder_fused") t.fused_step = value;
+    else if (k == "host_taper") sfa::host_tuning().taper = value;
+    else if (k == "host_heavy") sfa::host_tuning().heavy = value;
+    else if (k == "host_taper_bytes") sfa::host_tuning().taper_bytes = value > 0 ? value : 1;
+    else if (k == "host_piece_bytes") sfa::host_tuning().piece_bytes = value > 0 ? value : 1;
+    else if (k == "host_trace") sfa::host_tuning().trace = value;
     else return sfa::fail(SFA_ERR_INVALID, "sfa_tuning_set: unknown switch " + k);
     return SFA_OK;
 }

@@ -6,14 +6,21 @@
 // host->device copy of piece i+1, the kernel of piece i and the device->host copy of piece i-1 run at the
 // same time on three streams (PCIe is full duplex), so a call costs about max(upload, download) + one piece.
 //
-// Prefill pieces are (batch entry, block of query rows), all heads: with every head in a piece the host rows are
-// contiguous, so each piece moves as plain 1-D copies (a caller that owns a slice of heads - a rank of the multi-GPU
-// driver - passes strided tensors and the same code issues pitched 2-D copies).  Under the causal mask a piece of rows
-// [r0, r1) needs keys [0, r1 + shift) only, so K/V travel incrementally, piece by piece, and the first kernel
-// starts after the first piece's upload; the kernel's bottom-right aligned mask makes "rows [r0, r1) against the
-// key prefix" exactly the rows of the full problem.
+// Prefill pieces are (batch entry, group of kv-heads, block of query rows).  With every head in a piece the host rows
+// are contiguous, so each piece moves as plain 1-D copies (a caller that owns a slice of heads - a rank of the
+// multi-GPU driver - passes strided tensors and the same code issues pitched 2-D copies).  Under the causal mask a
+// piece of rows [r0, r1) needs keys [0, r1 + shift) only, so K/V travel incrementally, piece by piece, and the first
+// kernel starts after the first piece's upload; the kernel's bottom-right aligned mask makes "rows [r0, r1) against
+// the key prefix" exactly the rows of the full problem.
+//
+// What a call costs beyond its upload is the last piece's kernel and download plus ~28 us of copy-engine idle time
+// per piece (tools/e2e_pieces.py: C3 31.8 ms with 16 uniform pieces, 33.9 with 64, 38.2 with 256).  So the default
+// plan is FEW LARGE pieces with geometrically smaller ones at the end of the call, and the staging buffers form rings
+// (4 deep for Q / O / LSE, 3 for a unit's K/V) so that the upload never waits for the kernel two pieces back.
 #include "internal.h"
 
+#include <algorithm>
+#include <atomic>
 #include <math.h>
 #include <mutex>
 #include <vector>
@@ -21,19 +28,25 @@
 namespace sfa {
 namespace {
 
+constexpr int kRing = 4;      // staging slots per kind (Q, O, LSE): the upload may run this many pieces ahead of the kernels
+constexpr int kKvRing = 3;    // K/V staging slots (one per unit in flight)
+
 struct Pipeline {
     std::mutex mu;                   // one call at a time enqueues on a device's pipeline
     bool ready = false;
     bool used = false;               // ev_last has been recorded: the next call orders itself behind it
     cudaStream_t s_in = nullptr, s_out = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {}, ev_kv_done[2] = {};
-    // staging: [0..1] double buffers per kind; grown on demand, outgrown buffers are retired (work may be queued)
-    void* buf[8] = {};
-    size_t cap[8] = {};
+    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[kRing] = {}, ev_comp[kRing] = {}, ev_out[kRing] = {}, ev_kv_done[kKvRing] = {};
+    // staging rings; grown on demand, outgrown buffers are retired (work may be queued on them)
+    void* buf[16] = {};
+    size_t cap[16] = {};
     std::vector<void*> retired;
+    std::vector<cudaEvent_t> trace;   // host_trace: 5 timing events per piece of the last call (see fwd_host_trace)
 };
-enum { kQ0 = 0, kQ1, kO0, kO1, kKV0, kKV1, kL0, kL1 };   // Q, O, K+V, LSE (decode: q+seqlens, o+lse, caches)
+enum { kQ0 = 0, kO0 = kRing, kL0 = 2 * kRing, kKV0 = 3 * kRing, kNumBufs = 3 * kRing + kKvRing };   // Q, O, LSE, K+V (decode: q+seqlens, o+lse, -, caches)
+static_assert(kNumBufs <= 16, "staging table too small");
 
+std::atomic<int> g_last_plan_pieces{0};   // pieces of the most recent sfa_fwd_host plan (tests, tools)
 std::mutex g_pipes_mu;
 std::vector<Pipeline*> g_pipes;
 
@@ -50,8 +63,9 @@ int pipeline_init(Pipeline& p) {
     if (p.ready) return SFA_OK;
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
-    cudaEvent_t* evs[] = {&p.ev_start, &p.ev_last, &p.ev_in[0], &p.ev_in[1], &p.ev_comp[0], &p.ev_comp[1], &p.ev_out[0], &p.ev_out[1],
-                          &p.ev_kv_done[0], &p.ev_kv_done[1]};
+    std::vector<cudaEvent_t*> evs = {&p.ev_start, &p.ev_last};
+    for (int i = 0; i < kRing; ++i) { evs.push_back(&p.ev_in[i]); evs.push_back(&p.ev_comp[i]); evs.push_back(&p.ev_out[i]); }
+    for (int i = 0; i < kKvRing; ++i) evs.push_back(&p.ev_kv_done[i]);
     for (cudaEvent_t* e : evs) SFA_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     p.ready = true;
     return SFA_OK;
@@ -88,6 +102,98 @@ int check_pinned(const void* p, const char* what) {
 
 }  // namespace
 
+// ---- plan: pieces = (batch entry, group of kv-heads, block of query rows), in issue order
+// With many batch entries a unit is one entry with ALL its heads (contiguous on the host).  With few entries (one
+// long sequence) the heads are cut into groups first: under the causal mask the work of a block of rows grows
+// with its position while its upload does not, so row blocks alone leave the heavy last blocks' kernels behind
+// the end of the upload (C5, one sequence: 38.9 ms against a 30.1 ms copy floor); head groups are independent and
+// uniform.  A group keeps at least 1 KB per row and tensor (pitched DMAs slow down below that).
+std::vector<HostPiece> plan_fwd_host(int B, int Sq, int Sk, int Hq, int Hkv, int D, bool causal, int want_pieces) {
+    std::vector<HostPiece> plan;
+    if (B <= 0 || Sq <= 0 || Hkv <= 0 || Hq % Hkv) return plan;
+    const size_t es = 2;
+    const double in_bytes = es * ((double)B * Sq * Hq * D + 2.0 * B * Sk * Hkv * D);
+    const bool explicit_pieces = want_pieces > 0;
+    const HostTuning& tune = host_tuning();
+    if (want_pieces <= 0) {
+        want_pieces = 8;                                          // + the tapered end below
+        const int by_size = (int)(in_bytes / tune.piece_bytes);   // pieces of at least 8 MB keep the DMAs efficient
+        if (want_pieces > by_size) want_pieces = by_size > B ? by_size : B;
+    }
+    const int hg_min = (int)(1024 / (D * es)) > 0 ? (int)(1024 / (D * es)) : 1;
+    int n_hg = 1;
+    if (B < 4) {
+        n_hg = Hkv / hg_min;
+        if (n_hg > want_pieces / B) n_hg = want_pieces / B;
+        if (n_hg < 1) n_hg = 1;
+    }
+    const int hg = (Hkv + n_hg - 1) / n_hg;               // kv-heads per group
+    n_hg = (Hkv + hg - 1) / hg;
+    const int grp = Hq / Hkv;
+    // Estimated kernel time against upload time.  A "heavy" call (C5: 29 ms of kernels, 29 ms of copies) is bound by
+    // the SUM of its kernels, and small pieces of causal work do not fill the GPU (2 kv-heads x 8192 rows are 64 work
+    // items for 148 SMs; a tapered C5 plan measured 34.4 - 34.6 ms like the uniform one, its 2-head units taking 3.1
+    // and 3.6 ms of kernels against 1.95 for half of a 4-head unit): heavy calls keep uniform pieces.  A light call
+    // (C3: 3.5 ms of kernels) only needs a short tail.
+    const double flops = 4.0 * B * Hq * (double)Sq * Sk * D * (causal ? 0.5 : 1.0);
+    bool heavy = flops / 1.1e15 > 0.4 * in_bytes / 50e9;
+    if (tune.heavy >= 0) heavy = tune.heavy != 0;
+    const bool taper = !explicit_pieces && tune.taper != 0 && !heavy;
+    std::vector<int> groups;                               // kv-heads per head group of one batch entry
+    {
+        // light calls: half groups at the two ends (nothing computes during the first upload, nothing uploads during
+        // the last kernel)
+        const int edge = hg / 2;
+        if (taper && n_hg >= 3 && edge >= 1 && Hkv - 2 * edge >= hg) {
+            groups.push_back(edge);
+            for (int left = Hkv - 2 * edge; left > 0; left -= hg) groups.push_back(left < hg ? left : hg);
+            groups.push_back(edge);
+        } else {
+            for (int left = Hkv; left > 0; left -= hg) groups.push_back(left < hg ? left : hg);
+        }
+    }
+    const int n_units = B * (int)groups.size();
+    // head groups of a long sequence are big, uniform pieces (C5: 4 heads x 65536 rows, a 3.3 ms kernel that keeps the
+    // GPU as busy as the full problem does), cut into two row blocks when the call is heavy (C5 on one GPU, staging
+    // rings 4 deep: 8 pieces 34.6 ms, 16 pieces 33.4 - 34.7, 32 pieces 34.9, 64 pieces 34.7; with the two-deep staging
+    // of the first version 16 pieces cost 39.0: the upload waited for the kernel two pieces back)
+    const int target = (n_hg > 1 && !explicit_pieces) ? (heavy ? 2 * B * n_hg : 8) : want_pieces;
+    int n_r = (target + B * n_hg - 1) / (B * n_hg);
+    int rows_per = (Sq + n_r - 1) / n_r;
+    rows_per = (rows_per + 255) / 256 * 256;              // whole 256-row blocks of the kernel
+    n_r = (Sq + rows_per - 1) / rows_per;
+    // row cuts of a unit: uniform blocks; the last block of the LAST unit of a tapered plan is cut again into 1/2,
+    // 1/4, 1/8, 1/8 (the exposed tail is then the kernel and download of a small piece).  A refined piece keeps at
+    // least `taper_bytes` of input.
+    auto cuts_of = [&](bool last_unit, size_t bytes_per_row) {
+        std::vector<int> c;
+        for (int r = 0; r < n_r; ++r) c.push_back(r * rows_per);
+        c.push_back(Sq);
+        if (!taper || !last_unit) return c;
+        int a0 = c[c.size() - 2];
+        for (int level = 0; level < 3; ++level) {
+            const int len = Sq - a0;
+            const int half = (len / 2 + 255) / 256 * 256;
+            if (half <= 0 || half >= len || (size_t)(len - half) * bytes_per_row < (size_t)tune.taper_bytes) break;
+            a0 += half;                                   // the big part first
+            c.push_back(a0);
+        }
+        std::sort(c.begin(), c.end());
+        c.erase(std::unique(c.begin(), c.end()), c.end());
+        return c;
+    };
+    int unit = 0;
+    for (int b = 0; b < B; ++b) {
+        int hk0 = 0;
+        for (size_t g = 0; g < groups.size(); hk0 += groups[g], ++g, ++unit) {
+            const int hkn = groups[g];
+            const std::vector<int> cuts = cuts_of(unit == n_units - 1, ((size_t)hkn * grp + 2 * (size_t)hkn) * D * es);
+            for (size_t r = 0; r + 1 < cuts.size(); ++r) plan.push_back({b, hk0, hkn, cuts[r], cuts[r + 1], unit});
+        }
+    }
+    return plan;
+}
+
 int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     if (!a.q || !a.k || !a.v || !a.o) return fail(SFA_ERR_INVALID, "fwd_host: null tensor pointer");
     if (a.batch < 0 || a.seqlen_q < 0 || a.seqlen_k < 0 || a.heads_q <= 0 || a.heads_kv <= 0 || a.heads_q % a.heads_kv)
@@ -111,48 +217,34 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     Pipeline& P = *pp;
     if ((rc = pipeline_init(P))) return rc;
 
-    // ---- plan: pieces = (batch entry, group of kv-heads, block of query rows)
-    // With many batch entries a piece is a block of rows of ALL heads (contiguous on the host).  With few entries
-    // (one long sequence) the heads are cut into groups first: under the causal mask the work of a block of rows
-    // grows with its position while its upload does not, so row blocks alone leave the heavy last blocks' kernels
-    // behind the end of the upload (C5, one sequence: 38.9 ms against a 30.1 ms copy floor); head groups are
-    // independent and uniform.  A group keeps at least 1 KB per row and tensor (pitched DMAs slow down below that).
     const size_t es = 2;
-    const double in_bytes = es * ((double)B * Sq * Hq * D + 2.0 * B * Sk * Hkv * D);
-    const bool explicit_pieces = want_pieces > 0;
-    if (want_pieces <= 0) {
-        // 32 pieces: the last piece's kernel and download are exposed; pieces of at least 8 MB keep the DMAs efficient
-        want_pieces = 32;
-        const int by_size = (int)(in_bytes / (8 << 20));
-        if (want_pieces > by_size) want_pieces = by_size > B ? by_size : B;
-    }
-    const int hg_min = (int)(1024 / (D * es)) > 0 ? (int)(1024 / (D * es)) : 1;
-    int n_hg = 1;
-    if (B < 4) {
-        n_hg = Hkv / hg_min;
-        if (n_hg > want_pieces / B) n_hg = want_pieces / B;
-        if (n_hg < 1) n_hg = 1;
-    }
-    const int hg = (Hkv + n_hg - 1) / n_hg;               // kv-heads per group
-    n_hg = (Hkv + hg - 1) / hg;
     const int grp = Hq / Hkv;
-    // head groups of a long sequence are big, uniform pieces (C5: 4 heads x 65536 rows, a 3.3 ms kernel that keeps the
-    // GPU as busy as the full problem does); cutting them into row blocks as well only makes the kernels small and
-    // uneven, and here the kernel time is as long as the copy time
-    const int target = (n_hg > 1 && !explicit_pieces) ? 8 : want_pieces;   // (16: C5 on one GPU 39.0 ms against 34.6 with 8)
-    int n_r = (target + B * n_hg - 1) / (B * n_hg);
-    int rows_per = (Sq + n_r - 1) / n_r;
-    rows_per = (rows_per + 255) / 256 * 256;              // whole 256-row blocks of the kernel
-    n_r = (Sq + rows_per - 1) / rows_per;
+    const std::vector<HostPiece> plan = plan_fwd_host(B, Sq, Sk, Hq, Hkv, D, a.causal != 0, want_pieces);
+    int rows_max = 0, hg_max = 0, n_units = 0;
+    for (const HostPiece& pc : plan) {
+        rows_max = std::max(rows_max, pc.r1 - pc.r0);
+        hg_max = std::max(hg_max, pc.hkn);
+        n_units = std::max(n_units, pc.unit + 1);
+    }
     const int shift = Sk - Sq;
-    const size_t q_row_max = (size_t)hg * grp * D * es, kv_row_max = (size_t)hg * D * es;
+    const size_t q_row_max = (size_t)hg_max * grp * D * es, kv_row_max = (size_t)hg_max * D * es;
     const size_t kv_half = ((size_t)Sk * kv_row_max + 255) / 256 * 256;
-    if ((rc = ensure(P, kQ0, rows_per * q_row_max)) || (rc = ensure(P, kQ1, rows_per * q_row_max)) ||
-        (rc = ensure(P, kO0, rows_per * q_row_max)) || (rc = ensure(P, kO1, rows_per * q_row_max)) ||
-        (rc = ensure(P, kKV0, 2 * kv_half + 256)) || (rc = ensure(P, kL0, (size_t)hg * grp * rows_per * 4)) ||
-        (rc = ensure(P, kL1, (size_t)hg * grp * rows_per * 4)))
-        return rc;
-    if (B * n_hg > 1 && (rc = ensure(P, kKV1, 2 * kv_half + 256))) return rc;
+    for (int i = 0; i < kRing; ++i)
+        if ((rc = ensure(P, kQ0 + i, rows_max * q_row_max)) || (rc = ensure(P, kO0 + i, rows_max * q_row_max)) ||
+            (rc = ensure(P, kL0 + i, (size_t)hg_max * grp * rows_max * 4)))
+            return rc;
+    for (int i = 0; i < kKvRing && i < n_units; ++i)
+        if ((rc = ensure(P, kKV0 + i, 2 * kv_half + 256))) return rc;
+    const bool tracing = host_tuning().trace != 0;
+    if (tracing) {
+        for (cudaEvent_t e : P.trace) cudaEventDestroy(e);
+        P.trace.clear();
+    }
+    auto mark = [&](cudaStream_t st) {   // host_trace only: a timing event on `st`
+        if (!tracing) return;
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, st); P.trace.push_back(e); }
+    };
 
     // the previous call (maybe on another stream) may still be using the staging buffers
     if (P.used) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_last, 0));
@@ -163,78 +255,85 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     const uint8_t* hk = reinterpret_cast<const uint8_t*>(a.k);
     const uint8_t* hv = reinterpret_cast<const uint8_t*>(a.v);
     uint8_t* ho = reinterpret_cast<uint8_t*>(a.o);
-    int piece = 0, unit = 0;
-    bool comp_used[2] = {false, false}, out_used[2] = {false, false}, kv_used[2] = {false, false};
-    for (int b = 0; b < B; ++b) {
-        for (int g = 0; g < n_hg; ++g, ++unit) {
-            const int hk0 = g * hg, hkn = (Hkv - hk0 < hg) ? Hkv - hk0 : hg;      // kv-heads [hk0, hk0 + hkn)
-            const int hq0 = hk0 * grp, hqn = hkn * grp;
-            const size_t q_row = (size_t)hqn * D * es, kv_row = (size_t)hkn * D * es;
-            const int kvb = unit & 1;
-            uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + kvb]);
-            uint8_t* dV = dK + kv_half;
-            // this K/V buffer was last read by the kernels of the unit before the previous one
+    bool comp_used[kRing] = {}, out_used[kRing] = {}, kv_used[kKvRing] = {};
+    int keys_up = 0;   // keys of the current unit already on the device
+    for (size_t piece = 0; piece < plan.size(); ++piece) {
+        const HostPiece& pc = plan[piece];
+        const int b = pc.b, hk0 = pc.hk0, hkn = pc.hkn;                    // kv-heads [hk0, hk0 + hkn)
+        const int hq0 = hk0 * grp, hqn = hkn * grp;
+        const size_t q_row = (size_t)hqn * D * es, kv_row = (size_t)hkn * D * es;
+        const int kvb = pc.unit % kKvRing;
+        uint8_t* dK = reinterpret_cast<uint8_t*>(P.buf[kKV0 + kvb]);
+        uint8_t* dV = dK + kv_half;
+        if (piece == 0 || plan[piece - 1].unit != pc.unit) {
+            // this K/V buffer was last read by the kernels of the unit kKvRing units back
             if (kv_used[kvb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb], 0));
-            int keys_up = 0;   // keys of this unit already on the device
-            for (int r = 0; r < n_r; ++r, ++piece) {
-                const int r0 = r * rows_per, r1 = Sq < r0 + rows_per ? Sq : r0 + rows_per, rows = r1 - r0;
-                int keys = a.causal ? r1 + shift : Sk;       // keys [0, keys) are visible to rows < r1
-                keys = keys < 0 ? 0 : (keys > Sk ? Sk : keys);
-                const int pb = piece & 1;
-                uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
-                uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
-                float* dL = reinterpret_cast<float*>(P.buf[kL0 + pb]);
-                // ---- upload: the piece's Q rows and the K/V rows it is the first to need
-                if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
-                if ((rc = copy_rows(dQ, q_row, hq + es * ((size_t)b * a.q_batch_stride + (size_t)r0 * a.q_row_stride + (size_t)hq0 * D),
-                                    es * a.q_row_stride, q_row, rows, cudaMemcpyHostToDevice, P.s_in)))
-                    return rc;
-                if (keys > keys_up) {
-                    const size_t n = (size_t)(keys - keys_up);
-                    if ((rc = copy_rows(dK + keys_up * kv_row, kv_row,
-                                        hk + es * ((size_t)b * a.k_batch_stride + (size_t)keys_up * a.k_row_stride + (size_t)hk0 * D),
-                                        es * a.k_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)) ||
-                        (rc = copy_rows(dV + keys_up * kv_row, kv_row,
-                                        hv + es * ((size_t)b * a.v_batch_stride + (size_t)keys_up * a.v_row_stride + (size_t)hk0 * D),
-                                        es * a.v_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)))
-                        return rc;
-                    keys_up = keys;
-                }
-                SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
-                // ---- kernel
-                SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
-                if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
-                sfa_fwd_args d = {};
-                d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
-                d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = hqn; d.heads_kv = hkn; d.head_dim = D;
-                d.q_batch_stride = (int64_t)rows * hqn * D; d.q_row_stride = (int64_t)hqn * D; d.q_head_stride = D;
-                d.k_batch_stride = (int64_t)Sk * hkn * D; d.k_row_stride = (int64_t)hkn * D; d.k_head_stride = D;
-                d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
-                d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
-                d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
-                if ((rc = launch_fwd(d, cur))) return rc;
-                SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
-                comp_used[pb] = true;
-                // ---- download
-                SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
-                if ((rc = copy_rows(ho + es * ((size_t)b * a.o_batch_stride + (size_t)r0 * a.o_row_stride + (size_t)hq0 * D),
-                                    es * a.o_row_stride, dO, q_row, q_row, rows, cudaMemcpyDeviceToHost, P.s_out)))
-                    return rc;
-                if (a.lse)   // host (batch, heads, Sq) fp32: one row of `rows` floats per head
-                    if ((rc = copy_rows(a.lse + ((size_t)b * Hq + hq0) * Sq + r0, (size_t)Sq * 4, dL, (size_t)rows * 4,
-                                        (size_t)rows * 4, hqn, cudaMemcpyDeviceToHost, P.s_out)))
-                        return rc;
-                SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
-                out_used[pb] = true;
-            }
+            keys_up = 0;
+        }
+        const int r0 = pc.r0, r1 = pc.r1, rows = r1 - r0;
+        int keys = a.causal ? r1 + shift : Sk;       // keys [0, keys) are visible to rows < r1
+        keys = keys < 0 ? 0 : (keys > Sk ? Sk : keys);
+        const int pb = (int)(piece % kRing);
+        uint8_t* dQ = reinterpret_cast<uint8_t*>(P.buf[kQ0 + pb]);
+        uint8_t* dO = reinterpret_cast<uint8_t*>(P.buf[kO0 + pb]);
+        float* dL = reinterpret_cast<float*>(P.buf[kL0 + pb]);
+        // ---- upload: the piece's Q rows and the K/V rows it is the first to need
+        if (comp_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_comp[pb], 0));
+        mark(P.s_in);
+        if ((rc = copy_rows(dQ, q_row, hq + es * ((size_t)b * a.q_batch_stride + (size_t)r0 * a.q_row_stride + (size_t)hq0 * D),
+                            es * a.q_row_stride, q_row, rows, cudaMemcpyHostToDevice, P.s_in)))
+            return rc;
+        if (keys > keys_up) {
+            const size_t n = (size_t)(keys - keys_up);
+            if ((rc = copy_rows(dK + keys_up * kv_row, kv_row,
+                                hk + es * ((size_t)b * a.k_batch_stride + (size_t)keys_up * a.k_row_stride + (size_t)hk0 * D),
+                                es * a.k_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)) ||
+                (rc = copy_rows(dV + keys_up * kv_row, kv_row,
+                                hv + es * ((size_t)b * a.v_batch_stride + (size_t)keys_up * a.v_row_stride + (size_t)hk0 * D),
+                                es * a.v_row_stride, kv_row, n, cudaMemcpyHostToDevice, P.s_in)))
+                return rc;
+            keys_up = keys;
+        }
+        mark(P.s_in);
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
+        // ---- kernel
+        SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
+        if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
+        sfa_fwd_args d = {};
+        d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
+        d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = hqn; d.heads_kv = hkn; d.head_dim = D;
+        d.q_batch_stride = (int64_t)rows * hqn * D; d.q_row_stride = (int64_t)hqn * D; d.q_head_stride = D;
+        d.k_batch_stride = (int64_t)Sk * hkn * D; d.k_row_stride = (int64_t)hkn * D; d.k_head_stride = D;
+        d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
+        d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
+        d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
+        mark(cur);
+        if ((rc = launch_fwd(d, cur))) return rc;
+        mark(cur);
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
+        comp_used[pb] = true;
+        // ---- download
+        SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
+        if ((rc = copy_rows(ho + es * ((size_t)b * a.o_batch_stride + (size_t)r0 * a.o_row_stride + (size_t)hq0 * D),
+                            es * a.o_row_stride, dO, q_row, q_row, rows, cudaMemcpyDeviceToHost, P.s_out)))
+            return rc;
+        if (a.lse)   // host (batch, heads, Sq) fp32: one row of `rows` floats per head
+            if ((rc = copy_rows(a.lse + ((size_t)b * Hq + hq0) * Sq + r0, (size_t)Sq * 4, dL, (size_t)rows * 4,
+                                (size_t)rows * 4, hqn, cudaMemcpyDeviceToHost, P.s_out)))
+                return rc;
+        mark(P.s_out);
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
+        out_used[pb] = true;
+        if (piece + 1 == plan.size() || plan[piece + 1].unit != pc.unit) {
             SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb], cur));
             kv_used[kvb] = true;
         }
     }
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < kRing; ++i)
         if (out_used[i]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[i], 0));
     SFA_CUDA_CHECK(cudaEventRecord(P.ev_last, cur));
     P.used = true;
+    g_last_plan_pieces = (int)plan.size();
     return SFA_OK;
 }
 
@@ -332,6 +431,29 @@ int decode_host_impl(const sfa_decode_args& a, int want_pieces, cudaStream_t cur
     return SFA_OK;
 }
 
+HostTuning& host_tuning() {
+    static HostTuning t;
+    return t;
+}
+
+int host_last_plan_pieces() { return g_last_plan_pieces.load(); }
+
+// host_trace: milliseconds from the first upload's start to (upload start, upload end, kernel start, kernel end,
+// download end) of every piece of the last sfa_fwd_host call on the current device; returns the number of pieces.
+int fwd_host_trace(float* out, int capacity) {
+    Pipeline* pp = pipeline_for_current_device();
+    if (!pp) return 0;
+    std::lock_guard<std::mutex> lk(pp->mu);
+    if (cudaDeviceSynchronize() != cudaSuccess) return fail(SFA_ERR_CUDA, "fwd_host_trace: device synchronize failed");
+    const int n = (int)pp->trace.size() / 5;
+    for (int i = 0; i < n * 5 && out && i < capacity * 5; ++i) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, pp->trace[0], pp->trace[i]);
+        out[i] = ms;
+    }
+    return n;
+}
+
 void release_host_pipelines() {
     std::lock_guard<std::mutex> lk(g_pipes_mu);
     int cur = -1;
@@ -342,7 +464,7 @@ void release_host_pipelines() {
         std::lock_guard<std::mutex> lk2(p->mu);
         cudaSetDevice((int)i);
         cudaDeviceSynchronize();
-        for (int b = 0; b < 8; ++b) {
+        for (int b = 0; b < 16; ++b) {
             if (p->buf[b]) cudaFree(p->buf[b]);
             p->buf[b] = nullptr;
             p->cap[b] = 0;

@@ -1,5 +1,6 @@
 // Internal host-side contracts between the translation units of libStarFlashAttention.so.
 #pragma once
+#include <vector>
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <cuda_bf16.h>
@@ -136,5 +137,21 @@ int fwd_probe_read(unsigned long long* out, int n);
 int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t stream);
 int decode_host_impl(const sfa_decode_args& a, int want_pieces, cudaStream_t stream);
 void release_host_pipelines();
+// Plan switches of sfa_fwd_host (sfa_tuning_set "host_taper", "host_heavy", "host_taper_bytes", "host_piece_bytes",
+// "host_trace"; tests lower the byte thresholds so that small shapes go through the tapered plan).
+struct HostTuning {
+    int taper = 1;                 // 0: uniform pieces only
+    int heavy = -1;                // -1: by the estimated kernel / copy ratio; 0 / 1: plan as a light / heavy call
+    int taper_bytes = 4 << 20;     // a refined piece keeps at least this much input
+    int piece_bytes = 8 << 20;     // the default plan has at most input bytes / piece_bytes pieces (and at least one per batch entry)
+    int trace = 0;                 // 1: timing events around every piece's upload, kernel and download (fwd_host_trace)
+};
+HostTuning& host_tuning();
+// One piece of the sfa_fwd_host plan: rows [r0, r1) of kv-heads [hk0, hk0 + hkn) of batch entry b; pieces of one
+// unit (b, head group) are consecutive and share the unit's K/V staging.  Pure host logic (no device needed).
+struct HostPiece { int b, hk0, hkn, r0, r1, unit; };
+std::vector<HostPiece> plan_fwd_host(int B, int Sq, int Sk, int Hq, int Hkv, int D, bool causal, int want_pieces);
+int host_last_plan_pieces();
+int fwd_host_trace(float* out, int capacity);
 
 }  // namespace sfa

@@ -401,7 +401,8 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
              lse: Optional[torch.Tensor] = None, device=None, chunks: Optional[int] = None):
     """Prefill forward on pinned HOST tensors: q (B,Sq,Hq,D), k/v (B,Sk,Hkv,D) -> (out, lse) in pinned host memory.
     q/k/v/out may be slices of the heads of larger tensors (a rank's share); lse is dense (B,Hq,Sq).
-    ``chunks``: number of pieces the call is cut into (default: about 16).
+    ``chunks``: number of uniform pieces the call is cut into (default: the library's own plan, see sfa_fwd_host in
+    include/star_flash_attn.h).
     Asynchronous: the results are complete once the current stream of ``device`` has been synchronised."""
     for t, n in ((q, "q"), (k, "k"), (v, "v")):
         _pinned(t, n)
@@ -433,6 +434,29 @@ def fwd_host(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = F
     with torch.cuda.device(dev):
         check(lib.sfa_fwd_host(h, _stream()))
     return out, lse
+
+
+def fwd_host_plan(batch: int, seqlen_q: int, seqlen_k: int, heads_q: int, heads_kv: int, head_dim: int,
+                  causal: bool = True, chunks: Optional[int] = None):
+    """The piece plan fwd_host follows for these dimensions: a list of (batch entry, first kv-head, kv-heads, first
+    row, end row, unit) in issue order (sfa_fwd_host_plan; pure host logic, needs no GPU)."""
+    import ctypes as C
+    h = _capi.FwdHostArgs()
+    a = h.t
+    a.batch, a.seqlen_q, a.seqlen_k, a.heads_q, a.heads_kv, a.head_dim = batch, seqlen_q, seqlen_k, heads_q, heads_kv, head_dim
+    a.causal = 1 if causal else 0
+    h.pieces = int(chunks) if chunks else 0
+    n = lib.sfa_fwd_host_plan(h, None, 0)
+    if n < 0:
+        check(n)
+    buf = (C.c_int32 * (6 * max(n, 1)))()
+    n = lib.sfa_fwd_host_plan(h, buf, n)
+    return [tuple(buf[6 * i:6 * i + 6]) for i in range(n)]
+
+
+def fwd_host_last_pieces() -> int:
+    """Diagnostics: number of pieces the most recent fwd_host call was cut into."""
+    return int(lib.sfa_fwd_host_last_pieces())
 
 
 def decode_host(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, seqlens: Optional[torch.Tensor] = None,

@@ -312,6 +312,35 @@ def test_fwd_host_row_pieces_match_device_path(causal, Sq, Sk, chunks):
     _check(o_h, lse_h, o_ref, lse_ref, dtype, "fwd_host rows", mag=mag)
 
 
+@pytest.mark.parametrize("B,H,Hkv,S,causal", [(1, 16, 16, 2048, True), (5, 4, 2, 1536, True), (1, 32, 16, 1024, False), (2, 16, 16, 1300, True)])
+@pytest.mark.parametrize("heavy", [0, 1])
+def test_fwd_host_default_plan_matches_device_path(tuning, B, H, Hkv, S, causal, heavy):
+    """The library's own plan (no explicit piece count): light calls get half head groups at the ends and geometrically
+    smaller row blocks at the end of the call, heavy calls uniform head groups of two row blocks; staging rings four
+    pieces deep.  The byte thresholds are lowered so that these small shapes are cut the way C3 / C5 are; every row
+    must still equal the single device-resident call bit for bit."""
+    import starflashattention_b200 as sfa
+    tuning("host_piece_bytes", 16 << 10, 8 << 20)
+    tuning("host_taper_bytes", 32 << 10, 4 << 20)
+    tuning("host_heavy", heavy, -1)      # 0: light kernels (C3-like plan), 1: heavy kernels (C5-like plan)
+    dtype = torch.bfloat16
+    plan = sfa.fwd_host_plan(B, S, S, H, Hkv, 128, causal=causal)
+    assert len(plan) >= 8
+    if not heavy:
+        assert len({p[4] - p[3] for p in plan}) >= 2                          # tapered: pieces of several sizes
+    q = _rand((B, S, H, 128), dtype, 91).pin_memory()
+    k = _rand((B, S, Hkv, 128), dtype, 92).pin_memory()
+    v = _rand((B, S, Hkv, 128), dtype, 93).pin_memory()
+    o_h, lse_h = sfa.fwd_host(q, k, v, causal=causal)
+    assert sfa.fwd_host_last_pieces() == len(plan)
+    o_h2, lse_h2 = sfa.fwd_host(q, k, v, causal=causal)                       # again: the rings are reused
+    o_d, lse_d = sfa.fwd(q.cuda(), k.cuda(), v.cuda(), causal=causal)
+    torch.cuda.synchronize()
+    assert torch.equal(o_h, o_d.cpu()) and torch.equal(lse_h, lse_d.cpu())
+    assert torch.equal(o_h2, o_h) and torch.equal(lse_h2, lse_h)
+    assert sfa.fwd_watchdog() == 0
+
+
 def test_fwd_host_head_slice_views():
     """A rank of the multi-GPU driver owns a range of heads of the host tensors: strided views in, strided view out
     (pitched DMAs); the other heads of the output tensor stay untouched."""
