@@ -220,13 +220,17 @@ def step_fn(sfa, shape, d, out):
     return lambda: sfa.decode(d["q"], d["k"], d["v"], d["seqlens"], out=out)
 
 
-def timed(fn, steps, dev, world, dist, flush=None):
-    """K calls between two CUDA events on the current stream (after a barrier + synchronise), max over ranks."""
+def timed(fn, steps, dev, world, dist, flush=None, spin=0):
+    """K calls between two CUDA events on the current stream (after a barrier + synchronise), max over ranks.
+    spin: device-side cycles to burn ahead of the first event, so that the host has every call enqueued before the
+    GPU reaches the timed region (calls of a few tens of microseconds would otherwise be timed at the host's pace)."""
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if flush is None:
+        if spin:
+            torch.cuda._sleep(int(spin))
         e0.record()
         for _ in range(steps):
             fn()
@@ -443,11 +447,14 @@ def secondary(sfa, primary, dev, peaks, world, rank, dist):
     """Device-resident timings of the other BASELINE configs, sharded like the primary (explanatory, not the
     headline): each with its own roofline object and clock samples.  At N=1 also the section-8(d) decode variants."""
     res = {}
-    cases = [("c4", None), ("c5", None)] + ([("c2", None), ("c4_b1_flushed", ("decode", torch.bfloat16, 1, 32, 8, 32768, 128, False)),
-                                             ("c4_b32", ("decode", torch.bfloat16, 32, 32, 8, 32768, 128, False))] if world == 1 else [])
+    # the power-hungry C5 goes last: the cases after it would run at the clocks the 1 kW cap leaves behind
+    cases = [("c4", None)] + ([("c2", None), ("c4_b1_flushed", ("decode", torch.bfloat16, 1, 32, 8, 32768, 128, False)),
+                               ("c4_b1_rotating", ("decode", torch.bfloat16, 1, 32, 8, 32768, 128, False)),
+                               ("c4_b32", ("decode", torch.bfloat16, 32, 32, 8, 32768, 128, False))] if world == 1 else []) + [("c5", None)]
     for name, custom in cases:
         if name == primary:
             continue
+        time.sleep(1.0)   # let the clocks recover from the case before (power cap): each line is measured from idle
         try:
             if custom is None:
                 shape, share = local_shape(name, world, rank)
@@ -471,13 +478,28 @@ def secondary(sfa, primary, dev, peaks, world, rank, dist):
             in_bytes = 2.0 * (q.numel() + k.numel() + v.numel())
             flush = ((torch.empty(256 << 20, dtype=torch.uint8, device=dev), torch.zeros(256 << 20, dtype=torch.uint8, device=dev))
                      if in_bytes < 400e6 else None)
+            l2_note = None
+            if name.endswith("_rotating"):
+                # back-to-back calls over several caches that together exceed L2: every call streams cold data, and
+                # the ~2 us granularity of a single event pair (the flushed line above) averages out over the calls
+                flush = None
+                n_sets = int(400e6 // in_bytes) + 2
+                ks, vs = [k] + [torch.randn_like(k) for _ in range(n_sets - 1)], [v] + [torch.randn_like(v) for _ in range(n_sets - 1)]
+                turn = [0]
+
+                def fn():
+                    i = turn[0] % n_sets
+                    turn[0] += 1
+                    return sfa.decode(q, ks[i], vs[i], sl, out=o_buf)
+                o_buf = torch.empty_like(q)
+                l2_note = f"{n_sets} caches of {in_bytes / 1e6:.0f} MB visited in turn by back-to-back calls (together larger than L2); all calls enqueued behind a device-side spin before the first event"
             for _ in range(3):
                 fn()
-            n = 20 if flush is not None else (5 if name == "c5" and world == 1 else 20)
+            n = 20 if flush is not None else (5 if name == "c5" and world == 1 else (96 if l2_note else 20))
             smp = ClockSampler(dev.index)
             if rank == 0:
                 smp.start()
-            ms_max, ms_own = timed(fn, n, dev, world, dist, flush=flush)
+            ms_max, ms_own = timed(fn, n, dev, world, dist, flush=flush, spin=8_000_000 if l2_note else 0)
             clk = smp.stop() if rank == 0 else None
             ms = ms_max / n
             rate = amount / (ms / 1e3)
@@ -485,11 +507,13 @@ def secondary(sfa, primary, dev, peaks, world, rank, dist):
             res[name] = {"metric": "attn_fwd_tflops" if kind == "fwd" else "decode_kv_gbs", "value": rate,
                          "unit": "TFLOP/s" if kind == "fwd" else "GB/s", "ms": ms, "steps": n,
                          "config": f"{kind} B={B} Hq={Hq} Hkv={Hkv} N={S} d={D} causal={causal}; {Bl} x {Hkvl} (batch x kv-head) per rank",
-                         "l2": "flushed before every call (256 MB written, then 256 MB read so that no dirty line is left)" if flush is not None else "inputs larger than L2",
+                         "l2": l2_note or ("flushed before every call (256 MB written, then 256 MB read so that no dirty line is left; one "
+                                           "event pair per call, ~2 us granularity)" if flush is not None else "inputs larger than L2"),
                          "roofline": {"bound": bound, "achieved": own, "peak": peaks[bound], "frac": own / peaks[bound],
                                       "unit": "TFLOP/s" if kind == "fwd" else "GB/s"},
                          "clocks": clk}
             del q, k, v
+            ks = vs = None
             torch.cuda.empty_cache()
         except Exception as e:  # noqa: BLE001 - a secondary line must not void the headline
             res[name] = {"error": repr(e)}

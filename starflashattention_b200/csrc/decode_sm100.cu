@@ -626,8 +626,20 @@ int choose_decode_splits(int batch, int heads_kv, int max_seqlen, int sm_count) 
             // ... and for very few units with a long cache (one sequence: 8 units, 74 splits each fill the 592 CTA slots
             // once): under ncu the split kernel takes 25.3 us with 72 splits against 28.1 - 28.5 with 48 or 128 and 32.9
             // with 96 (1.3 waves); the combine kernel costs 6 us either way (profiles/r2_fwd_tuning.md section 7)
+            // Which count near one wave: back-to-back calls over rotating caches (tools/decode_few_units.py,
+            // profiles/r2_decode_few_units.txt) put an EVEN cut first - 32768 keys: 64 splits 27.3 us, 72 27.7, 74 27.9;
+            // 65536 keys: 64 splits (1024-key chunks) 46.6 us, 74 (896) 47.0, 72 (960, 69 busy CTAs) 51.2 - so take the
+            // largest count in the upper quarter of the wave that cuts the cache into equal 64-key multiples, else the
+            // CTAs that a whole-8s count leaves busy (chunks are rounded up to 64 keys, the rest would start and idle)
             if (one_wave <= 96 && s > one_wave) {
-                const long w = one_wave / 8 * 8;   // whole 8s: even chunks
+                long w = 0;
+                for (long c = one_wave; c >= one_wave * 3 / 4 && c >= 2; --c)
+                    if (max_seqlen % (c * 64) == 0) { w = c; break; }
+                if (w == 0) {
+                    const long w8 = one_wave / 8 * 8 > 0 ? one_wave / 8 * 8 : one_wave;
+                    const long chunk = ((max_seqlen + w8 - 1) / w8 + 63) / 64 * 64;
+                    w = (max_seqlen + chunk - 1) / chunk;
+                }
                 return (int)(w < by_len ? w : by_len);
             }
         }
