@@ -460,6 +460,8 @@ int sfa_tuning_set(const char* name, int32_t value) {
     else if (k == "host_taper_bytes") sfa::host_tuning().taper_bytes = value > 0 ? value : 1;
     else if (k == "host_piece_bytes") sfa::host_tuning().piece_bytes = value > 0 ? value : 1;
     else if (k == "host_trace") sfa::host_tuning().trace = value;
+    else if (k == "host_kernel_streams") sfa::host_tuning().kernel_streams = value;
+    else if (k == "host_wave_items") sfa::host_tuning().wave_items = value > 0 ? value : 1;
     else return sfa::fail(SFA_ERR_INVALID, "sfa_tuning_set: unknown switch " + k);
     return SFA_OK;
 }

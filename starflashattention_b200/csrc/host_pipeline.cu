@@ -35,8 +35,8 @@ struct Pipeline {
     std::mutex mu;                   // one call at a time enqueues on a device's pipeline
     bool ready = false;
     bool used = false;               // ev_last has been recorded: the next call orders itself behind it
-    cudaStream_t s_in = nullptr, s_out = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[kRing] = {}, ev_comp[kRing] = {}, ev_out[kRing] = {}, ev_kv_done[kKvRing] = {};
+    cudaStream_t s_in = nullptr, s_out = nullptr, s_comp = nullptr;   // s_comp: second kernel stream (prefill pieces alternate)
+    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[kRing] = {}, ev_comp[kRing] = {}, ev_out[kRing] = {}, ev_kv_done[kKvRing][2] = {};
     // staging rings; grown on demand, outgrown buffers are retired (work may be queued on them)
     void* buf[16] = {};
     size_t cap[16] = {};
@@ -63,9 +63,10 @@ int pipeline_init(Pipeline& p) {
     if (p.ready) return SFA_OK;
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
+    SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_comp, cudaStreamNonBlocking));
     std::vector<cudaEvent_t*> evs = {&p.ev_start, &p.ev_last};
     for (int i = 0; i < kRing; ++i) { evs.push_back(&p.ev_in[i]); evs.push_back(&p.ev_comp[i]); evs.push_back(&p.ev_out[i]); }
-    for (int i = 0; i < kKvRing; ++i) evs.push_back(&p.ev_kv_done[i]);
+    for (int i = 0; i < kKvRing; ++i) { evs.push_back(&p.ev_kv_done[i][0]); evs.push_back(&p.ev_kv_done[i][1]); }
     for (cudaEvent_t* e : evs) SFA_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     p.ready = true;
     return SFA_OK;
@@ -153,12 +154,20 @@ std::vector<HostPiece> plan_fwd_host(int B, int Sq, int Sk, int Hq, int Hkv, int
         }
     }
     const int n_units = B * (int)groups.size();
-    // head groups of a long sequence are big, uniform pieces (C5: 4 heads x 65536 rows, a 3.3 ms kernel that keeps the
-    // GPU as busy as the full problem does), cut into two row blocks when the call is heavy (C5 on one GPU, staging
-    // rings 4 deep: 8 pieces 34.6 ms, 16 pieces 33.4 - 34.7, 32 pieces 34.9, 64 pieces 34.7; with the two-deep staging
-    // of the first version 16 pieces cost 39.0: the upload waited for the kernel two pieces back)
-    const int target = (n_hg > 1 && !explicit_pieces) ? (heavy ? 2 * B * n_hg : 8) : want_pieces;
+    // Row blocks.  Light calls: about 8 pieces in all.  Heavy calls: ONE WAVE of work items per kernel - a piece of
+    // hqn query heads x rows is hqn * rows / 256 items for the 148 persistent CTAs, and a launch of 172 items (4 heads x
+    // 11008 rows) runs a second, nearly empty wave: C5 on one GPU with two kernel streams, pieces of 4 heads x
+    // 32768 / 16384 / 11008 / 8192 / 5632 / 4096 rows: 33.5 / 34.1 / 37.3 / 32.8 / 36.0 / 38.0 ms; a rank's half of C5
+    // 18.7 / 18.4 / 19.0 / 17.7 / 19.7 / 30.2 (profiles/r2_ks_sweep.txt).  At most ~96 pieces per call.
+    const int target = (n_hg > 1 && !explicit_pieces) ? 8 : want_pieces;
     int n_r = (target + B * n_hg - 1) / (B * n_hg);
+    if (heavy && !explicit_pieces) {
+        int blocks = tune.wave_items / (hg * grp);
+        if (blocks < 1) blocks = 1;
+        n_r = (Sq + blocks * 256 - 1) / (blocks * 256);
+        const int cap = 96 / (B * n_hg) > 1 ? 96 / (B * n_hg) : 1;
+        if (n_r > cap) n_r = cap;
+    }
     int rows_per = (Sq + n_r - 1) / n_r;
     rows_per = (rows_per + 255) / 256 * 256;              // whole 256-row blocks of the kernel
     n_r = (Sq + rows_per - 1) / rows_per;
@@ -251,6 +260,11 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     SFA_CUDA_CHECK(cudaEventRecord(P.ev_start, cur));
     SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
     SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_start, 0));
+    // The pieces' kernels alternate between the caller's stream and a second one: they are independent, and a
+    // persistent kernel ends with SMs going idle one by one (its last, heaviest items) - the next piece's CTAs move in
+    // as they free up instead of waiting for the whole grid to drain.
+    const bool two_streams = host_tuning().kernel_streams != 1;
+    if (two_streams) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_comp, P.ev_start, 0));
     const uint8_t* hq = reinterpret_cast<const uint8_t*>(a.q);
     const uint8_t* hk = reinterpret_cast<const uint8_t*>(a.k);
     const uint8_t* hv = reinterpret_cast<const uint8_t*>(a.v);
@@ -267,7 +281,10 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         uint8_t* dV = dK + kv_half;
         if (piece == 0 || plan[piece - 1].unit != pc.unit) {
             // this K/V buffer was last read by the kernels of the unit kKvRing units back
-            if (kv_used[kvb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb], 0));
+            if (kv_used[kvb]) {
+                SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb][0], 0));
+                if (two_streams) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb][1], 0));
+            }
             keys_up = 0;
         }
         const int r0 = pc.r0, r1 = pc.r1, rows = r1 - r0;
@@ -297,8 +314,9 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         mark(P.s_in);
         SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
         // ---- kernel
-        SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_in[pb], 0));
-        if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(cur, P.ev_out[pb], 0));
+        cudaStream_t ks = (two_streams && (piece & 1)) ? P.s_comp : cur;
+        SFA_CUDA_CHECK(cudaStreamWaitEvent(ks, P.ev_in[pb], 0));
+        if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(ks, P.ev_out[pb], 0));
         sfa_fwd_args d = {};
         d.q = dQ; d.k = dK; d.v = dV; d.o = dO; d.lse = a.lse ? dL : nullptr;
         d.batch = 1; d.seqlen_q = rows; d.seqlen_k = keys; d.heads_q = hqn; d.heads_kv = hkn; d.head_dim = D;
@@ -307,10 +325,10 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         d.v_batch_stride = d.k_batch_stride; d.v_row_stride = d.k_row_stride; d.v_head_stride = D;
         d.o_batch_stride = d.q_batch_stride; d.o_row_stride = d.q_row_stride; d.o_head_stride = D;
         d.softmax_scale = a.softmax_scale; d.causal = a.causal; d.dtype = a.dtype;
-        mark(cur);
-        if ((rc = launch_fwd(d, cur))) return rc;
-        mark(cur);
-        SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], cur));
+        mark(ks);
+        if ((rc = launch_fwd(d, ks))) return rc;
+        mark(ks);
+        SFA_CUDA_CHECK(cudaEventRecord(P.ev_comp[pb], ks));
         comp_used[pb] = true;
         // ---- download
         SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_out, P.ev_comp[pb], 0));
@@ -325,7 +343,8 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
         out_used[pb] = true;
         if (piece + 1 == plan.size() || plan[piece + 1].unit != pc.unit) {
-            SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb], cur));
+            SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb][0], cur));
+            if (two_streams) SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb][1], P.s_comp));
             kv_used[kvb] = true;
         }
     }

@@ -144,6 +144,8 @@ struct HostTuning {
     int heavy = -1;                // -1: by the estimated kernel / copy ratio; 0 / 1: plan as a light / heavy call
     int taper_bytes = 4 << 20;     // a refined piece keeps at least this much input
     int piece_bytes = 8 << 20;     // the default plan has at most input bytes / piece_bytes pieces (and at least one per batch entry)
+    int wave_items = 128;          // heavy calls: work items (256-row blocks x query heads) per piece - one wave of the 148 CTAs
+    int kernel_streams = 2;        // 1: every piece's kernel on the caller's stream; 2: alternating with a second stream
     int trace = 0;                 // 1: timing events around every piece's upload, kernel and download (fwd_host_trace)
 };
 HostTuning& host_tuning();

@@ -316,13 +316,14 @@ def test_fwd_host_row_pieces_match_device_path(causal, Sq, Sk, chunks):
 @pytest.mark.parametrize("heavy", [0, 1])
 def test_fwd_host_default_plan_matches_device_path(tuning, B, H, Hkv, S, causal, heavy):
     """The library's own plan (no explicit piece count): light calls get half head groups at the ends and geometrically
-    smaller row blocks at the end of the call, heavy calls uniform head groups of two row blocks; staging rings four
-    pieces deep.  The byte thresholds are lowered so that these small shapes are cut the way C3 / C5 are; every row
+    smaller row blocks at the end of the call, heavy calls uniform head groups cut into row blocks of one wave of work
+    items each, their kernels alternating between two streams; staging rings four pieces deep.  The byte thresholds are lowered so that these small shapes are cut the way C3 / C5 are; every row
     must still equal the single device-resident call bit for bit."""
     import starflashattention_b200 as sfa
     tuning("host_piece_bytes", 16 << 10, 8 << 20)
     tuning("host_taper_bytes", 32 << 10, 4 << 20)
     tuning("host_heavy", heavy, -1)      # 0: light kernels (C3-like plan), 1: heavy kernels (C5-like plan)
+    tuning("host_wave_items", 8, 128)     # heavy plan: pieces of 8 work items instead of one wave of 128
     dtype = torch.bfloat16
     plan = sfa.fwd_host_plan(B, S, S, H, Hkv, 128, causal=causal)
     assert len(plan) >= 8

@@ -40,12 +40,14 @@ def test_default_plan_of_c3_and_c5():
     assert len(c3) <= 12
     assert all(r1 - r0 == 8192 for b, _, _, r0, r1, _ in c3 if b < 7)      # whole entries in the middle
     assert c3[-1][4] - c3[-1][3] <= 1024                                   # the exposed last piece is small
-    # a heavy call (kernels as long as the copies) keeps uniform 4-head groups, two row blocks each: small pieces of
-    # causal work would not fill the GPU
+    # a heavy call (kernels as long as the copies) keeps uniform 4-head groups, cut into row blocks of one wave of work
+    # items (4 heads x 8192 rows = 128 items for the 148 persistent CTAs)
     c5 = sfa.fwd_host_plan(1, 65536, 65536, 32, 32, 128)
-    assert len(c5) == 16 and all(p[2] == 4 and p[4] - p[3] == 32768 for p in c5)
+    assert len(c5) == 64 and all(p[2] == 4 and p[4] - p[3] == 8192 for p in c5)
     c5_half = sfa.fwd_host_plan(1, 65536, 65536, 16, 16, 128)
-    assert len(c5_half) == 8 and all(p[2] == 4 and p[4] - p[3] == 32768 for p in c5_half)
+    assert len(c5_half) == 32 and all(p[2] == 4 and p[4] - p[3] == 8192 for p in c5_half)
+    c5_eighth = sfa.fwd_host_plan(1, 65536, 65536, 4, 4, 128)
+    assert len(c5_eighth) == 8 and all(p[2] == 4 and p[4] - p[3] == 8192 for p in c5_eighth)
 
 
 def test_explicit_piece_count_is_uniform_and_switch_turns_taper_off():

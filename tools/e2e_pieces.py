@@ -54,6 +54,10 @@ def main():
 
     print(f"[e2e_pieces] {name} plain-copy floor (up || down) median {wall(floor)[0]:.2f} ms, upload alone {wall(up_only)[0]:.2f} ms", flush=True)
     anatomy(name, B, Hq, Hkv, S, D, causal, q, k, v, out, lse, dq, dk, dv, do, wall)
+    for ks in (1, 2, 1, 2):
+        sfa.tuning_set("host_kernel_streams", ks)
+        med, mn = wall(lambda: sfa.fwd_host(q, k, v, causal=causal, out=out, lse=lse))
+        print(f"[e2e_pieces] {name} default plan, kernels on {ks} stream(s): median {med:.2f} ms  min {mn:.2f} ms", flush=True)
     for pieces in (0, 8, 16, 32, 64):
         med, mn = wall(lambda: sfa.fwd_host(q, k, v, causal=causal, out=out, lse=lse, chunks=pieces or None))
         print(f"[e2e_pieces] {name} pieces={pieces or 'default'} median {med:.2f} ms  min {mn:.2f} ms", flush=True)
