@@ -307,7 +307,7 @@ int sfa_fwd_probe_read(uint64_t* out, int32_t n);
  * "host_taper" (0: sfa_fwd_host cuts uniform pieces only), "host_heavy" (-1 auto / 0 / 1: plan the call as one whose
  * kernels are short / as long as its copies), "host_taper_bytes" (smallest refined piece, default 4 MiB),
  * "host_piece_bytes" (the default plan has at most input bytes / this many pieces, default 8 MiB), "host_trace",
- * "host_kernel_streams" (2: the pieces' kernels alternate between `stream` and a library stream; 1: all on `stream`),
+ * "host_kernel_streams" (1 .. 4 kernel streams the pieces take turns on, the first being `stream`; default 2),
  * "host_wave_items" (work items per piece of a heavy call, default 128).
  * None of them changes the arithmetic contract; not thread-safe against concurrent launches. */
 int sfa_tuning_set(const char* name, int32_t value);

@@ -35,8 +35,8 @@ struct Pipeline {
     std::mutex mu;                   // one call at a time enqueues on a device's pipeline
     bool ready = false;
     bool used = false;               // ev_last has been recorded: the next call orders itself behind it
-    cudaStream_t s_in = nullptr, s_out = nullptr, s_comp = nullptr;   // s_comp: second kernel stream (prefill pieces alternate)
-    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[kRing] = {}, ev_comp[kRing] = {}, ev_out[kRing] = {}, ev_kv_done[kKvRing][2] = {};
+    cudaStream_t s_in = nullptr, s_out = nullptr, s_comp[3] = {};   // s_comp: extra kernel streams (prefill pieces take turns)
+    cudaEvent_t ev_start = nullptr, ev_last = nullptr, ev_in[kRing] = {}, ev_comp[kRing] = {}, ev_out[kRing] = {}, ev_kv_done[kKvRing][4] = {};
     // staging rings; grown on demand, outgrown buffers are retired (work may be queued on them)
     void* buf[16] = {};
     size_t cap[16] = {};
@@ -63,10 +63,11 @@ int pipeline_init(Pipeline& p) {
     if (p.ready) return SFA_OK;
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
     SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
-    SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_comp, cudaStreamNonBlocking));
+    for (int i = 0; i < 3; ++i) SFA_CUDA_CHECK(cudaStreamCreateWithFlags(&p.s_comp[i], cudaStreamNonBlocking));
     std::vector<cudaEvent_t*> evs = {&p.ev_start, &p.ev_last};
     for (int i = 0; i < kRing; ++i) { evs.push_back(&p.ev_in[i]); evs.push_back(&p.ev_comp[i]); evs.push_back(&p.ev_out[i]); }
-    for (int i = 0; i < kKvRing; ++i) { evs.push_back(&p.ev_kv_done[i][0]); evs.push_back(&p.ev_kv_done[i][1]); }
+    for (int i = 0; i < kKvRing; ++i)
+        for (int j = 0; j < 4; ++j) evs.push_back(&p.ev_kv_done[i][j]);
     for (cudaEvent_t* e : evs) SFA_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     p.ready = true;
     return SFA_OK;
@@ -263,8 +264,9 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
     // The pieces' kernels alternate between the caller's stream and a second one: they are independent, and a
     // persistent kernel ends with SMs going idle one by one (its last, heaviest items) - the next piece's CTAs move in
     // as they free up instead of waiting for the whole grid to drain.
-    const bool two_streams = host_tuning().kernel_streams != 1;
-    if (two_streams) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_comp, P.ev_start, 0));
+    int n_ks = host_tuning().kernel_streams;
+    n_ks = n_ks < 1 ? 1 : (n_ks > 4 ? 4 : n_ks);
+    for (int i = 1; i < n_ks; ++i) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_comp[i - 1], P.ev_start, 0));
     const uint8_t* hq = reinterpret_cast<const uint8_t*>(a.q);
     const uint8_t* hk = reinterpret_cast<const uint8_t*>(a.k);
     const uint8_t* hv = reinterpret_cast<const uint8_t*>(a.v);
@@ -282,8 +284,7 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         if (piece == 0 || plan[piece - 1].unit != pc.unit) {
             // this K/V buffer was last read by the kernels of the unit kKvRing units back
             if (kv_used[kvb]) {
-                SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb][0], 0));
-                if (two_streams) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb][1], 0));
+                for (int i = 0; i < n_ks; ++i) SFA_CUDA_CHECK(cudaStreamWaitEvent(P.s_in, P.ev_kv_done[kvb][i], 0));
             }
             keys_up = 0;
         }
@@ -314,7 +315,8 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         mark(P.s_in);
         SFA_CUDA_CHECK(cudaEventRecord(P.ev_in[pb], P.s_in));
         // ---- kernel
-        cudaStream_t ks = (two_streams && (piece & 1)) ? P.s_comp : cur;
+        const int ki = (int)(piece % n_ks);
+        cudaStream_t ks = ki == 0 ? cur : P.s_comp[ki - 1];
         SFA_CUDA_CHECK(cudaStreamWaitEvent(ks, P.ev_in[pb], 0));
         if (out_used[pb]) SFA_CUDA_CHECK(cudaStreamWaitEvent(ks, P.ev_out[pb], 0));
         sfa_fwd_args d = {};
@@ -343,8 +345,7 @@ int fwd_host_impl(const sfa_fwd_args& a, int want_pieces, cudaStream_t cur) {
         SFA_CUDA_CHECK(cudaEventRecord(P.ev_out[pb], P.s_out));
         out_used[pb] = true;
         if (piece + 1 == plan.size() || plan[piece + 1].unit != pc.unit) {
-            SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb][0], cur));
-            if (two_streams) SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb][1], P.s_comp));
+            for (int i = 0; i < n_ks; ++i) SFA_CUDA_CHECK(cudaEventRecord(P.ev_kv_done[kvb][i], i == 0 ? cur : P.s_comp[i - 1]));
             kv_used[kvb] = true;
         }
     }

@@ -145,7 +145,7 @@ struct HostTuning {
     int taper_bytes = 4 << 20;     // a refined piece keeps at least this much input
     int piece_bytes = 8 << 20;     // the default plan has at most input bytes / piece_bytes pieces (and at least one per batch entry)
     int wave_items = 128;          // heavy calls: work items (256-row blocks x query heads) per piece - one wave of the 148 CTAs
-    int kernel_streams = 2;        // 1: every piece's kernel on the caller's stream; 2: alternating with a second stream
+    int kernel_streams = 2;        // kernel streams the pieces take turns on (1 .. 4; the first is the caller's)
     int trace = 0;                 // 1: timing events around every piece's upload, kernel and download (fwd_host_trace)
 };
 HostTuning& host_tuning();
