@@ -17,6 +17,10 @@
  *                         prologue, extended to GQA / bf16 / LSE        src/flash_attn.cu:554-935
  *   sfa_fwd            <- no reference counterpart (the reference has no prefill kernel);
  *                         softmax(QK^T*scale [+causal])V as in examples/python/testFlashDecoder.py:84-92
+ *   sfa_fwd_host,      <- the launcher's own host<->device traffic (blocking cudaMemcpy + cudaDeviceSynchronize per
+ *   sfa_decode_host       call)                                          src/flash_attn.cu:973-975,986
+ *   sfa_decode_static  <- no reference counterpart: a decode entry that allocates
+ *                         nothing
  * The C++-mangled drop-in symbols (run_flash_decoder<half>, compute_rotary_table<half>,
  * init_half_array) are exported from the same library; see include/src/flash_attn.h.
  */
