@@ -112,7 +112,7 @@ int check_pinned(const void* p, const char* what) {
 // uniform.  A group keeps at least 1 KB per row and tensor (pitched DMAs slow down below that).
 std::vector<HostPiece> plan_fwd_host(int B, int Sq, int Sk, int Hq, int Hkv, int D, bool causal, int want_pieces) {
     std::vector<HostPiece> plan;
-    if (B <= 0 || Sq <= 0 || Hkv <= 0 || Hq % Hkv) return plan;
+    if (B <= 0 || Sq <= 0 || Sk < 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv || D <= 0) return plan;
     const size_t es = 2;
     const double in_bytes = es * ((double)B * Sq * Hq * D + 2.0 * B * Sk * Hkv * D);
     const bool explicit_pieces = want_pieces > 0;

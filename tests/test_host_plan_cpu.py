@@ -59,3 +59,8 @@ def test_explicit_piece_count_is_uniform_and_switch_turns_taper_off():
     finally:
         sfa.tuning_set("host_taper", 1)
     assert len(flat) == 8 and all(p[3] == 0 and p[4] == 8192 for p in flat)
+
+
+def test_plan_of_degenerate_dimensions_is_empty():
+    for shape in [(0, 8, 8, 4, 4, 128), (2, 0, 8, 4, 4, 128), (2, 8, 8, 4, 4, 0), (2, 8, 8, 0, 4, 128), (2, 8, 8, 4, 3, 128)]:
+        assert sfa.fwd_host_plan(*shape) == []
