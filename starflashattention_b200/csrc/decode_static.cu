@@ -57,6 +57,7 @@ int sfa_decode_static(const sfa_decode_args* args, void* stream) {
     sfa_decode_args a = *args;
     a.workspace = nullptr;
     a.workspace_bytes = 0;
+    if (a.batch <= 0 || a.heads_q <= 0 || a.heads_kv <= 0 || a.head_dim <= 0) return sfa_decode(&a, stream);   // nothing to size: its checks answer
     // split count and scratch size exactly as sfa_decode would choose them
     const int splits = sfa_decode_num_splits(&a);
     if (splits < 0) return splits;
